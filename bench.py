@@ -1,0 +1,369 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark: block-parallel Snappy (PIM-compression multi-block format).
+
+Workload (BASELINE.json configs[4], the configuration the metric is quoted on): a synthetic
+64 GiB corpus of 64 independent 1 GiB SYN-MIX streams (1 MiB text-like / 1 MiB random
+alternating, 32 KB blocks) sharded over 8 B200 -- i.e. 8 streams (8 GiB) per GPU.  Weak scaling:
+every rank always works on 8 GiB (fewer only if --streams-per-gpu says so or memory forces it;
+the JSON line states what ran).
+
+One step = compress + decompress of every stream of the rank.
+  value  device-resident: inputs, offsets and outputs in HBM, kernels only (CUDA events)
+  e2e    the same through the reference-facing C ABI (snappy_compress_dpu/snappy_decompress_dpu)
+         on pinned HOST buffers, H2D and D2H inside the timed region
+  --impl reference   the reference's own host codec (oracle/_ref, else the oracle port) on the
+         box's host cores, all threads, on a bounded sample of the same streams.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GIB = 1 << 30
+SEED_BASE = 0x64000000
+METRIC = "uncompressed GB/s, compress + decompress round trip (block-parallel Snappy)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--streams-per-gpu", type=int, default=8)
+    ap.add_argument("--stream-bytes", type=int, default=GIB)
+    ap.add_argument("--block-size", type=int, default=32768)
+    ap.add_argument("--cpu-sample-mib", type=int, default=1024, help="cpu_baseline sample size (1 thread)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def workload_name(args, n_gpus):
+    return (f"SYN-MIX corpus, {n_gpus * args.streams_per_gpu} streams x {args.stream_bytes / GIB:g} GiB "
+            f"({n_gpus * args.streams_per_gpu * args.stream_bytes / GIB:g} GiB total, {args.streams_per_gpu} streams per GPU), "
+            f"{args.block_size} B blocks, contiguous block ranges per GPU")
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        # samples under load = the upper half of the clock readings
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU legs
+def cpu_codec():
+    from oracle.oracle import Oracle, Reference
+    if Reference.available():
+        return Reference(), "reference"
+    return Oracle(), "port"
+
+
+def cpu_baseline_1thread(P, args):
+    """Reference host codec, as-is (single thread), on a bounded sample of stream 0."""
+    codec, kind = cpu_codec()
+    n = min(args.cpu_sample_mib << 20, args.stream_bytes)
+    data = P.synth_host(P.SYNTH_MIX, SEED_BASE, n)
+    t0 = time.perf_counter()
+    comp = codec.compress(data, args.block_size)
+    t1 = time.perf_counter()
+    rc, back = codec.decompress(comp)
+    t2 = time.perf_counter()
+    assert rc == 0 and back.size == n
+    return {"value": n / (t2 - t0) / 1e9, "unit": "GB/s", "cores": 1, "kind": kind,
+            "sample": f"first {n >> 20} MiB of stream 0 (SYN-MIX), compress {n / (t1 - t0) / 1e9:.3f} GB/s + decompress {n / (t2 - t1) / 1e9:.3f} GB/s, 1 thread",
+            "compress_gbps": n / (t1 - t0) / 1e9, "decompress_gbps": n / (t2 - t1) / 1e9}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's host codec on all host threads (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import pim_compression_b200 as P
+    from concurrent.futures import ThreadPoolExecutor
+    P.lib()
+    codec, kind = cpu_codec()
+    cores = len(os.sched_getaffinity(0))
+    slice_bytes = 32 << 20  # one independent stream slice per thread per step
+    slices = [P.synth_host(P.SYNTH_MIX, SEED_BASE + t, slice_bytes) for t in range(cores)]
+
+    def work(d):
+        c = codec.compress(d, args.block_size)
+        rc, b = codec.decompress(c)
+        assert rc == 0 and b.size == d.size
+        return d.size
+
+    times = []
+    with ThreadPoolExecutor(cores) as ex:
+        for it in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            total = sum(ex.map(work, slices))
+            dt = time.perf_counter() - t0
+            if it >= args.warmup:
+                times.append(dt)
+    t = sum(times) / len(times)
+    v = total / t / 1e9
+    sample = f"{cores} threads x {slice_bytes >> 20} MiB SYN-MIX slices per step, compress + decompress each (ctypes releases the GIL)"
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic", "config": {"workload": workload_name(args, args.gpus)},
+            "cpu_baseline": {"value": v, "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def mem_available_bytes():
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return int(ln.split()[1]) * 1024
+    except Exception:
+        pass
+    return 0
+
+
+def run_ours(args):
+    import ctypes as C
+    import numpy as np
+    import torch
+    import pim_compression_b200 as P
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    L = P.lib()
+    assert P.set_devices([local_rank]) == 1, "no usable sm_100 GPU"
+
+    S, n, bs = args.streams_per_gpu, args.stream_bytes, args.block_size
+    nb = int(L.pim_snappy_num_blocks(n, bs))
+    st = torch.cuda.current_stream().cuda_stream
+
+    # ---- resident inputs: stream s of this rank is global stream rank*S+s of the corpus
+    d_in = []
+    for s in range(S):
+        t = torch.empty(n, dtype=torch.uint8, device=dev)
+        P.synth_device(P.SYNTH_MIX, SEED_BASE + rank * S + s, t.data_ptr(), n, st)
+        d_in.append(t)
+    scratch = torch.empty(int(L.pim_snappy_compress_scratch_bytes(n, bs)), dtype=torch.uint8, device=dev)
+    d_comp = torch.empty(int(L.pim_snappy_compress_bound(n, bs)), dtype=torch.uint8, device=dev)
+    d_off = torch.empty(nb + 1, dtype=torch.int64, device=dev)
+    d_back = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_status = torch.zeros(1, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+
+    def device_step():
+        for s in range(S):
+            P.compress_device(d_in[s].data_ptr(), n, bs, scratch.data_ptr(), scratch.numel(), d_comp.data_ptr(), d_off.data_ptr(), st)
+            P.decompress_device(d_comp.data_ptr(), d_off.data_ptr(), nb, bs, n, d_back.data_ptr(), d_status.data_ptr(), st)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- warm-up + one correctness check (round trip of the last stream; compressed sizes)
+    comp_bytes = 0
+    for w in range(max(args.warmup, 1)):
+        if w == 0:
+            for s in range(S):
+                P.compress_device(d_in[s].data_ptr(), n, bs, scratch.data_ptr(), scratch.numel(), d_comp.data_ptr(), d_off.data_ptr(), st)
+                P.decompress_device(d_comp.data_ptr(), d_off.data_ptr(), nb, bs, n, d_back.data_ptr(), d_status.data_ptr(), st)
+                torch.cuda.synchronize()
+                comp_bytes += int(d_off[-1].item())
+                assert int(d_status.item()) == 0 and torch.equal(d_back, d_in[s]), f"round trip failed on stream {s}"
+        else:
+            device_step()
+    U = S * n
+
+    # ---- timed region, device resident
+    sampler = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ else local_rank)
+    sync_all()
+    P.profile(True)
+    P.profile_read()
+    launches0 = P.launch_count()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        device_step()
+    e1.record()
+    sync_all()
+    dev_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    clocks = sampler.stop()
+    launches = P.launch_count() - launches0
+    prof = P.profile_read()
+    P.profile(False)
+
+    total_U = sum_over_ranks(U)
+    value = total_U / (dev_ms * 1e-3) / 1e9
+    peak, peak_src = peaks()
+    kern = {}
+    for k in ("compress", "decompress"):
+        ms = prof[k]["ms"] / max(prof[k]["launches"], 1)  # per launch = per stream
+        alg = n + comp_bytes / S                            # U + C per launch
+        kern[k] = {"ms_per_launch": ms, "uncompressed_gbps": n / (ms * 1e-3) / 1e9, "achieved_gbps": alg / (ms * 1e-3) / 1e9,
+                   "frac_of_hbm_peak": alg / (ms * 1e-3) / 1e9 / peak, "launches": prof[k]["launches"]}
+    dom = max(("compress", "decompress"), key=lambda k: prof[k]["ms"])
+    roofline = {"kernel": f"snappy_{dom}_kernel", "bound": "hbm", "achieved": kern[dom]["achieved_gbps"], "peak": peak,
+                "unit": "GB/s", "frac": kern[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": n + comp_bytes / S,
+                "share_of_step": prof[dom]["ms"] / (e0.elapsed_time(e1))}
+
+    # ---- end to end through the C ABI on pinned host buffers
+    e2e = None
+    if not args.no_e2e:
+        avail = mem_available_bytes()
+        per_stream = n
+        fixed = int(L.pim_snappy_compress_bound(n, bs)) + 64 + n + 4096
+        distinct = S
+        if avail:
+            budget = avail // max(world, 1) // 2
+            distinct = int(max(1, min(S, (budget - fixed) // per_stream)))
+        h_in = [P.PinnedBuffer(n) for _ in range(distinct)]
+        for s in range(distinct):
+            torch.from_numpy(h_in[s].array).copy_(d_in[s])
+        h_comp = P.PinnedBuffer(int(L.pim_snappy_compress_bound(n, bs)) + 64)
+        h_back = P.PinnedBuffer(n + 4096)
+        torch.cuda.synchronize()
+
+        def e2e_stream(s):
+            inp, out, rt = P.HostBufferContext(), P.HostBufferContext(), P.ProgramRuntime()
+            inp.buffer = inp.curr = h_in[s % distinct].ptr
+            inp.length, inp.max, out.max = n, 2**63, 2**63
+            out.buffer = out.curr = h_comp.ptr
+            rc = L.snappy_compress_dpu(C.byref(inp), C.byref(out), bs, C.byref(rt))
+            assert rc == 0, f"snappy_compress_dpu rc={rc}"
+            clen = int(out.length)
+            # what setup_decompression does, minus its allocation: consume the length varint
+            hdr = bytes(h_comp.array[:5])
+            k = next(i for i in range(5) if not hdr[i] & 0x80) + 1
+            dinp, dout = P.HostBufferContext(), P.HostBufferContext()
+            dinp.buffer, dinp.curr, dinp.length, dinp.max = h_comp.ptr, h_comp.ptr + k, clen, 2**63
+            dout.buffer = dout.curr = h_back.ptr
+            dout.length, dout.max = n, 2**63
+            rc = L.snappy_decompress_dpu(C.byref(dinp), C.byref(dout), C.byref(rt))
+            assert rc == 0, f"snappy_decompress_dpu rc={rc}"
+            return clen
+
+        for _ in range(max(1, min(args.warmup, 2))):
+            clens = [e2e_stream(s) for s in range(S)]
+        assert np.array_equal(h_back.array[:n], h_in[(S - 1) % distinct].array), "e2e round trip mismatch"
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            for s in range(S):
+                e2e_stream(s)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0) / args.steps
+        sync_all()
+        csum = sum(clens)
+        e2e = {"value": total_U / dt / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(U + csum), "d2h_bytes_per_step": int(csum + U),
+               "ms_per_step": dt * 1e3, "distinct_host_streams": distinct,
+               "api": "snappy_compress_dpu + snappy_decompress_dpu (C ABI) on page-locked host buffers, one GPU per rank"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_1thread(P, args)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
+                "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+                "data": "synthetic",
+                "config": {"workload": workload_name(args, world), "l2": "inputs (8 GiB per GPU) far exceed the 126 MB L2; no flush needed",
+                           "compressed_fraction": comp_bytes / U, "bytes_per_gpu": U},
+                "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,588 @@
+// C-ABI shim: the reference's DPU entry points, served by B200 GPUs.
+//
+//   snappy_compress_dpu    replaces snappy/snappy_compress.c:487-714
+//   snappy_decompress_dpu  replaces snappy/snappy_decompress.c:292-493
+//   setup_compression      replaces snappy/snappy_compress.c:418-453
+//   setup_decompression    replaces snappy/snappy_decompress.c:187-215
+//
+// Like the reference, the work is split into contiguous block ranges, one per device
+// (snappy_compress.c:494-520, snappy_decompress.c:306-340) -- here one host thread and one
+// CUDA stream per GPU, no inter-GPU traffic, and a host-side stitch of the compressed shards
+// (snappy_compress.c:697-703).  There is no CPU codec in this library: if no usable GPU is
+// present the entry points fail.
+
+#include <algorithm>
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <thread>
+#include <vector>
+#include <atomic>
+
+#include "common.cuh"
+
+namespace pimsnappy {
+
+static std::atomic<uint64_t> g_launches{0};
+void note_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- per-kernel event timing --------------------------------------------------
+static std::atomic<int> g_prof{0};
+static std::mutex g_prof_mu;
+struct ProfSpan { int which; cudaEvent_t a, b; };
+static std::vector<ProfSpan> g_spans;       // completed begin/end pairs awaiting a read
+static cudaEvent_t g_open[4] = {nullptr, nullptr, nullptr, nullptr};
+
+void prof_begin(int which, cudaStream_t st)
+{
+	if (!g_prof.load(std::memory_order_relaxed))
+		return;
+	std::lock_guard<std::mutex> lk(g_prof_mu);
+	cudaEvent_t e;
+	if (cudaEventCreate(&e) != cudaSuccess)
+		return;
+	cudaEventRecord(e, st);
+	g_open[which] = e;
+}
+
+void prof_end(int which, cudaStream_t st)
+{
+	if (!g_prof.load(std::memory_order_relaxed))
+		return;
+	std::lock_guard<std::mutex> lk(g_prof_mu);
+	if (!g_open[which])
+		return;
+	cudaEvent_t e;
+	if (cudaEventCreate(&e) != cudaSuccess)
+		return;
+	cudaEventRecord(e, st);
+	g_spans.push_back({which, g_open[which], e});
+	g_open[which] = nullptr;
+}
+
+namespace {
+
+double now_s()
+{
+	using namespace std::chrono;
+	return duration<double>(steady_clock::now().time_since_epoch()).count();
+}
+
+// ---- pinned host allocations made through pim_snappy_host_alloc -------------
+std::mutex g_alloc_mu;
+std::map<void *, size_t> g_allocs;
+
+size_t owned_capacity(const void *p) // capacity from p to the end of our allocation, 0 if not ours
+{
+	std::lock_guard<std::mutex> lk(g_alloc_mu);
+	auto it = g_allocs.upper_bound(const_cast<void *>(p));
+	if (it == g_allocs.begin())
+		return 0;
+	--it;
+	const uint8_t *base = static_cast<const uint8_t *>(it->first);
+	const uint8_t *q = static_cast<const uint8_t *>(p);
+	if (q >= base + it->second)
+		return 0;
+	return it->second - (size_t)(q - base);
+}
+
+// ---- devices ----------------------------------------------------------------
+struct DeviceCtx {
+	int dev = -1;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+	// grow-only device buffers, reused across calls
+	uint8_t *d_a = nullptr; size_t cap_a = 0;       // uncompressed side
+	uint8_t *d_b = nullptr; size_t cap_b = 0;       // compressed side
+	uint8_t *d_scratch = nullptr; size_t cap_s = 0; // compress slots + sizes
+	uint64_t *d_off = nullptr; size_t cap_off = 0;  // block offsets (entries)
+	uint32_t *d_status = nullptr;
+	uint64_t *h_small = nullptr;                    // pinned: [0] total, [1] status
+};
+
+std::mutex g_dev_mu;
+std::vector<DeviceCtx> g_devs;
+bool g_devs_ready = false;
+
+bool device_usable(int id)
+{
+	cudaDeviceProp p;
+	if (cudaGetDeviceProperties(&p, id) != cudaSuccess)
+		return false;
+	return p.major >= 10; // the kernels are compiled for sm_100a only
+}
+
+int init_devices_locked(const int *ids, int n)
+{
+	for (auto &d : g_devs) {
+		if (d.dev < 0)
+			continue;
+		cudaSetDevice(d.dev);
+		if (d.stream) cudaStreamDestroy(d.stream);
+		for (auto &e : d.ev) if (e) cudaEventDestroy(e);
+		cudaFree(d.d_a); cudaFree(d.d_b); cudaFree(d.d_scratch); cudaFree(d.d_off); cudaFree(d.d_status);
+		if (d.h_small) cudaFreeHost(d.h_small);
+	}
+	g_devs.clear();
+	std::vector<int> want;
+	if (ids && n > 0) {
+		want.assign(ids, ids + n);
+	} else {
+		int count = 0;
+		if (cudaGetDeviceCount(&count) != cudaSuccess)
+			count = 0;
+		if (const char *e = getenv("PIM_SNAPPY_NR_GPUS")) {
+			int lim = atoi(e);
+			if (lim > 0 && lim < count)
+				count = lim;
+		}
+		for (int i = 0; i < count; i++)
+			want.push_back(i);
+	}
+	for (int id : want) {
+		if (!device_usable(id)) {
+			fprintf(stderr, "pim_snappy: CUDA device %d is not an sm_100-class GPU; skipped\n", id);
+			continue;
+		}
+		DeviceCtx d;
+		d.dev = id;
+		if (cudaSetDevice(id) != cudaSuccess) continue;
+		if (cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess) continue;
+		for (auto &e : d.ev) cudaEventCreate(&e);
+		cudaMalloc(&d.d_status, 256);
+		cudaHostAlloc(&d.h_small, 256, cudaHostAllocDefault);
+		g_devs.push_back(d);
+	}
+	g_devs_ready = true;
+	return (int)g_devs.size();
+}
+
+int ensure_devices()
+{
+	std::lock_guard<std::mutex> lk(g_dev_mu);
+	if (!g_devs_ready)
+		init_devices_locked(nullptr, 0);
+	return (int)g_devs.size();
+}
+
+template <typename T>
+bool grow(T *&p, size_t &cap, size_t need)
+{
+	if (need <= cap)
+		return true;
+	if (p)
+		cudaFree(p);
+	p = nullptr;
+	cap = 0;
+	need = (need + (need >> 3) + 4095) & ~size_t(4095);
+	if (cudaMalloc(&p, need * sizeof(T)) != cudaSuccess) {
+		fprintf(stderr, "pim_snappy: cudaMalloc(%zu) failed\n", need * sizeof(T));
+		return false;
+	}
+	cap = need;
+	return true;
+}
+
+size_t put_varint32(uint8_t *p, uint32_t v) // snappy_compress.c:69-98
+{
+	size_t k = 0;
+	while (v >= 0x80) {
+		p[k++] = (uint8_t)(v | 0x80);
+		v >>= 7;
+	}
+	p[k++] = (uint8_t)v;
+	return k;
+}
+
+bool get_varint32(const uint8_t *&p, const uint8_t *end, uint32_t *v) // snappy_decompress.c:23-37
+{
+	uint32_t acc = 0;
+	for (int k = 0; k < 5 && p < end; k++) {
+		const uint8_t c = *p++;
+		acc |= (uint32_t)(c & 0x7F) << (7 * k);
+		if (!(c & 0x80)) {
+			*v = acc;
+			return true;
+		}
+	}
+	return false;
+}
+
+struct ShardTimes {
+	float copy_in = 0, run = 0, copy_out = 0; // ms
+	double alloc = 0;                         // s
+};
+
+// contiguous block range of shard g out of ng (snappy_compress.c:495)
+void shard_range(uint64_t nblocks, int ng, int g, uint64_t *lo, uint64_t *hi)
+{
+	const uint64_t per = (nblocks + ng - 1) / ng;
+	*lo = std::min(nblocks, per * (uint64_t)g);
+	*hi = std::min(nblocks, *lo + per);
+}
+
+template <typename F>
+void for_each_shard(int ng, F &&fn)
+{
+	if (ng == 1) {
+		fn(0);
+		return;
+	}
+	std::vector<std::thread> th;
+	for (int g = 0; g < ng; g++)
+		th.emplace_back([&, g] { fn(g); });
+	for (auto &t : th)
+		t.join();
+}
+
+} // namespace
+} // namespace pimsnappy
+
+using namespace pimsnappy;
+
+// ------------------------------------------------------------------------ misc
+
+extern "C" const char *pim_snappy_version(void) { return "pim-compression_b200 0.1 (sm_100a)"; }
+extern "C" uint64_t pim_snappy_launch_count(void) { return g_launches.load(); }
+
+extern "C" void pim_snappy_profile(int enable) { g_prof.store(enable ? 1 : 0); }
+
+extern "C" int pim_snappy_profile_read(double ms[4], uint64_t n[4])
+{
+	std::lock_guard<std::mutex> lk(g_prof_mu);
+	for (int i = 0; i < 4; i++) {
+		ms[i] = 0;
+		n[i] = 0;
+	}
+	int rc = 0;
+	for (auto &s : g_spans) {
+		float t = 0;
+		if (cudaEventSynchronize(s.b) == cudaSuccess && cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess) {
+			ms[s.which] += t;
+			n[s.which] += 1;
+		} else {
+			rc = 1;
+		}
+		cudaEventDestroy(s.a);
+		cudaEventDestroy(s.b);
+	}
+	g_spans.clear();
+	return rc;
+}
+
+extern "C" double get_runtime(struct timeval *start, struct timeval *end) // dpu_snappy.c:87-91
+{
+	return (double)(end->tv_sec - start->tv_sec) + (double)(end->tv_usec - start->tv_usec) / 1e6;
+}
+
+extern "C" void *pim_snappy_host_alloc(size_t bytes)
+{
+	void *p = nullptr;
+	if (bytes == 0)
+		bytes = 1;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+		cudaGetLastError();
+		return nullptr; // no pageable substitute: the caller sees the failure
+	}
+	std::lock_guard<std::mutex> lk(g_alloc_mu);
+	g_allocs[p] = bytes;
+	return p;
+}
+
+extern "C" void pim_snappy_host_free(void *p)
+{
+	if (!p)
+		return;
+	{
+		std::lock_guard<std::mutex> lk(g_alloc_mu);
+		g_allocs.erase(p);
+	}
+	cudaFreeHost(p);
+}
+
+extern "C" int pim_snappy_set_devices(const int *device_ids, int n)
+{
+	std::lock_guard<std::mutex> lk(g_dev_mu);
+	return init_devices_locked(device_ids, n);
+}
+
+extern "C" int pim_snappy_device_count(void) { return ensure_devices(); }
+
+// ----------------------------------------------------------------------- setup
+
+extern "C" void setup_compression(struct host_buffer_context *input, struct host_buffer_context *output, struct program_runtime *runtime)
+{
+	const double t0 = now_s();
+	// The reference allocates 32 + n + n/6 (snappy_compress.c:55-60,446-447), which forgets the
+	// 4-byte block headers; size for the smallest block size this library accepts being 1 would
+	// be 5n, so the bound is taken for block_size >= 64 and re-checked in snappy_compress_dpu.
+	const size_t n = input->length;
+	const size_t cap = 64 + n + n / 6 + 40 * (n / 64 + 1);
+	output->buffer = static_cast<uint8_t *>(pim_snappy_host_alloc(cap));
+	output->curr = output->buffer;
+	output->length = 0;
+	runtime->pre = now_s() - t0;
+}
+
+extern "C" snappy_status setup_decompression(struct host_buffer_context *input, struct host_buffer_context *output,
+                                             struct program_runtime *runtime)
+{
+	const double t0 = now_s();
+	uint32_t dlength = 0;
+	const uint8_t *p = input->curr;
+	if (!get_varint32(p, input->buffer + input->length, &dlength)) {
+		fprintf(stderr, "Failed to read decompressed length\n");
+		return SNAPPY_INVALID_INPUT;
+	}
+	input->curr = const_cast<uint8_t *>(p);
+	if (dlength > output->max) {
+		fprintf(stderr, "Output length is to big: max=%ld len=%d\n", output->max, dlength);
+		return SNAPPY_BUFFER_TOO_SMALL;
+	}
+	output->buffer = static_cast<uint8_t *>(pim_snappy_host_alloc(((size_t)dlength + 7) | 0x7FF));
+	if (!output->buffer)
+		return SNAPPY_INVALID_INPUT;
+	output->curr = output->buffer;
+	output->length = dlength;
+	runtime->pre = now_s() - t0;
+	return SNAPPY_OK;
+}
+
+// -------------------------------------------------------------------- compress
+
+extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, struct host_buffer_context *output, uint32_t block_size,
+                                             struct program_runtime *runtime)
+{
+	double t0 = now_s();
+	runtime->d_alloc = runtime->load = runtime->copy_in = runtime->run = runtime->copy_out = runtime->d_free = 0;
+	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE) {
+		fprintf(stderr, "pim_snappy: block size %u is outside the format's valid domain (1..%u)\n", block_size, PIM_SNAPPY_MAX_BLOCK_SIZE);
+		return SNAPPY_BUFFER_TOO_SMALL;
+	}
+	if (input->length > 0xFFFFFFFFul)
+		return SNAPPY_BUFFER_TOO_SMALL; // lengths are varint32 (snappy_compress.c:461)
+	if (!output->buffer)
+		return SNAPPY_INVALID_INPUT;
+
+	const uint64_t len = input->length;
+	const uint64_t nblocks = pim_snappy_num_blocks(len, block_size);
+	// capacity we may assume: ours if we allocated it, else the reference's own bound
+	size_t cap = owned_capacity(output->buffer);
+	if (cap == 0)
+		cap = len ? 32 + len + len / 6 : 16;
+
+	uint8_t hdr[16];
+	size_t hlen = put_varint32(hdr, (uint32_t)len); // snappy_compress.c:523-525
+	hlen += put_varint32(hdr + hlen, block_size);
+	if (cap < hlen)
+		return SNAPPY_BUFFER_TOO_SMALL;
+	memcpy(output->buffer, hdr, hlen);
+	output->curr = output->buffer + hlen;
+	output->length = hlen;
+	runtime->pre += now_s() - t0;
+
+	t0 = now_s();
+	int ng = ensure_devices();
+	runtime->load = now_s() - t0;
+	if (ng <= 0) {
+		fprintf(stderr, "pim_snappy: no usable sm_100 GPU; there is no CPU fallback\n");
+		return SNAPPY_INVALID_INPUT;
+	}
+	if (nblocks == 0)
+		return SNAPPY_OK;
+	if ((uint64_t)ng > nblocks)
+		ng = (int)nblocks;
+
+	std::vector<ShardTimes> tm(ng);
+	std::vector<uint64_t> total(ng, 0);
+	std::vector<int> rc(ng, SNAPPY_OK);
+
+	// phase 1: H2D + kernels + read back each shard's compressed size
+	for_each_shard(ng, [&](int g) {
+		DeviceCtx &d = g_devs[g];
+		uint64_t lo, hi;
+		shard_range(nblocks, ng, g, &lo, &hi);
+		const uint64_t in_lo = lo * (uint64_t)block_size;
+		const uint64_t in_bytes = std::min(len, hi * (uint64_t)block_size) - in_lo;
+		const uint64_t nb = hi - lo;
+		cudaSetDevice(d.dev);
+		const double a0 = now_s();
+		bool ok = grow(d.d_a, d.cap_a, in_bytes + 64) && grow(d.d_b, d.cap_b, pim_snappy_compress_bound(in_bytes, block_size)) &&
+		          grow(d.d_scratch, d.cap_s, pim_snappy_compress_scratch_bytes(in_bytes, block_size)) && grow(d.d_off, d.cap_off, nb + 1);
+		tm[g].alloc = now_s() - a0;
+		if (!ok) { rc[g] = SNAPPY_BUFFER_TOO_SMALL; return; }
+		cudaEventRecord(d.ev[0], d.stream);
+		cudaMemcpyAsync(d.d_a, input->buffer + in_lo, in_bytes, cudaMemcpyHostToDevice, d.stream);
+		cudaEventRecord(d.ev[1], d.stream);
+		rc[g] = pim_snappy_compress_device(d.d_a, in_bytes, block_size, d.d_scratch, d.cap_s, d.d_b, d.d_off, d.stream);
+		cudaEventRecord(d.ev[2], d.stream);
+		cudaMemcpyAsync(d.h_small, d.d_off + nb, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.stream);
+		if (cudaStreamSynchronize(d.stream) != cudaSuccess) {
+			fprintf(stderr, "pim_snappy: compress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+			rc[g] = SNAPPY_INVALID_INPUT;
+			return;
+		}
+		total[g] = d.h_small[0];
+		cudaEventElapsedTime(&tm[g].copy_in, d.ev[0], d.ev[1]);
+		cudaEventElapsedTime(&tm[g].run, d.ev[1], d.ev[2]);
+	});
+	for (int g = 0; g < ng; g++)
+		if (rc[g] != SNAPPY_OK)
+			return (snappy_status)rc[g];
+
+	// host-side stitch: shard g lands after the header and the shards before it
+	std::vector<uint64_t> at(ng + 1, hlen);
+	for (int g = 0; g < ng; g++)
+		at[g + 1] = at[g] + total[g];
+	if (at[ng] > cap) {
+		fprintf(stderr, "pim_snappy: compressed size %llu exceeds the output buffer (%zu)\n", (unsigned long long)at[ng], cap);
+		return SNAPPY_BUFFER_TOO_SMALL;
+	}
+
+	// phase 2: D2H straight into the final position
+	for_each_shard(ng, [&](int g) {
+		DeviceCtx &d = g_devs[g];
+		cudaSetDevice(d.dev);
+		cudaEventRecord(d.ev[0], d.stream);
+		cudaMemcpyAsync(output->buffer + at[g], d.d_b, total[g], cudaMemcpyDeviceToHost, d.stream);
+		cudaEventRecord(d.ev[1], d.stream);
+		if (cudaStreamSynchronize(d.stream) != cudaSuccess) {
+			rc[g] = SNAPPY_INVALID_INPUT;
+			return;
+		}
+		cudaEventElapsedTime(&tm[g].copy_out, d.ev[0], d.ev[1]);
+	});
+	for (int g = 0; g < ng; g++) {
+		if (rc[g] != SNAPPY_OK)
+			return (snappy_status)rc[g];
+		runtime->d_alloc = std::max(runtime->d_alloc, tm[g].alloc);
+		runtime->copy_in = std::max(runtime->copy_in, tm[g].copy_in * 1e-3);
+		runtime->run = std::max(runtime->run, tm[g].run * 1e-3);
+		runtime->copy_out = std::max(runtime->copy_out, tm[g].copy_out * 1e-3);
+	}
+	output->length = at[ng];
+	output->curr = output->buffer + at[ng];
+	return SNAPPY_OK;
+}
+
+// ------------------------------------------------------------------ decompress
+
+extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input, struct host_buffer_context *output,
+                                               struct program_runtime *runtime)
+{
+	double t0 = now_s();
+	runtime->d_alloc = runtime->load = runtime->copy_in = runtime->run = runtime->copy_out = runtime->d_free = 0;
+	const uint8_t *end = input->buffer + input->length;
+	const uint8_t *p = input->curr;
+	uint32_t block_size = 0;
+	if (!get_varint32(p, end, &block_size)) { // snappy_decompress.c:299-303
+		fprintf(stderr, "Failed to read decompressed block size\n");
+		return SNAPPY_INVALID_INPUT;
+	}
+	const uint64_t out_len = output->length;
+	if (out_len == 0)
+		return p == end ? SNAPPY_OK : SNAPPY_INVALID_INPUT;
+	if (block_size == 0)
+		return SNAPPY_INVALID_INPUT;
+	if (block_size > PIM_SNAPPY_MAX_BLOCK_SIZE) {
+		fprintf(stderr, "pim_snappy: block size %u is outside the format's valid domain (1..%u)\n", block_size, PIM_SNAPPY_MAX_BLOCK_SIZE);
+		return SNAPPY_BUFFER_TOO_SMALL;
+	}
+	if (!output->buffer)
+		return SNAPPY_INVALID_INPUT;
+	const uint64_t nblocks = pim_snappy_num_blocks(out_len, block_size);
+
+	// serial walk over the 4-byte block headers (snappy_decompress.c:317-340)
+	std::vector<uint64_t> off(nblocks + 1);
+	const uint8_t *body = p;
+	const uint64_t body_len = (uint64_t)(end - body);
+	uint64_t pos = 0;
+	for (uint64_t i = 0; i < nblocks; i++) {
+		if (pos + 4 > body_len)
+			return SNAPPY_INVALID_INPUT;
+		off[i] = pos;
+		const uint32_t cs = (uint32_t)body[pos] | ((uint32_t)body[pos + 1] << 8) | ((uint32_t)body[pos + 2] << 16) | ((uint32_t)body[pos + 3] << 24);
+		pos += 4 + (uint64_t)cs;
+		if (pos > body_len)
+			return SNAPPY_INVALID_INPUT;
+	}
+	off[nblocks] = pos;
+	if (pos != body_len)
+		return SNAPPY_INVALID_INPUT;
+	runtime->pre += now_s() - t0;
+
+	t0 = now_s();
+	int ng = ensure_devices();
+	runtime->load = now_s() - t0;
+	if (ng <= 0) {
+		fprintf(stderr, "pim_snappy: no usable sm_100 GPU; there is no CPU fallback\n");
+		return SNAPPY_INVALID_INPUT;
+	}
+	if ((uint64_t)ng > nblocks)
+		ng = (int)nblocks;
+
+	std::vector<ShardTimes> tm(ng);
+	std::vector<int> rc(ng, SNAPPY_OK);
+	for_each_shard(ng, [&](int g) {
+		DeviceCtx &d = g_devs[g];
+		uint64_t lo, hi;
+		shard_range(nblocks, ng, g, &lo, &hi);
+		const uint64_t nb = hi - lo;
+		const uint64_t c_lo = off[lo], c_bytes = off[hi] - off[lo];
+		const uint64_t o_lo = lo * (uint64_t)block_size;
+		const uint64_t o_bytes = std::min(out_len, hi * (uint64_t)block_size) - o_lo;
+		cudaSetDevice(d.dev);
+		const double a0 = now_s();
+		bool ok = grow(d.d_a, d.cap_a, o_bytes + 64) && grow(d.d_b, d.cap_b, c_bytes + 64) && grow(d.d_off, d.cap_off, nb + 1);
+		tm[g].alloc = now_s() - a0;
+		if (!ok) { rc[g] = SNAPPY_BUFFER_TOO_SMALL; return; }
+		std::vector<uint64_t> rel(nb + 1);
+		for (uint64_t i = 0; i <= nb; i++)
+			rel[i] = off[lo + i] - c_lo;
+		cudaEventRecord(d.ev[0], d.stream);
+		cudaMemcpyAsync(d.d_b, body + c_lo, c_bytes, cudaMemcpyHostToDevice, d.stream);
+		cudaMemcpyAsync(d.d_off, rel.data(), (nb + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d.stream);
+		cudaEventRecord(d.ev[1], d.stream);
+		rc[g] = pim_snappy_decompress_device(d.d_b, d.d_off, nb, block_size, o_bytes, d.d_a, d.d_status, d.stream);
+		cudaEventRecord(d.ev[2], d.stream);
+		cudaMemcpyAsync(output->buffer + o_lo, d.d_a, o_bytes, cudaMemcpyDeviceToHost, d.stream);
+		cudaMemcpyAsync(d.h_small + 1, d.d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, d.stream);
+		cudaEventRecord(d.ev[3], d.stream);
+		if (cudaStreamSynchronize(d.stream) != cudaSuccess) {
+			fprintf(stderr, "pim_snappy: decompress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+			rc[g] = SNAPPY_INVALID_INPUT;
+			return;
+		}
+		if (rc[g] == SNAPPY_OK && (uint32_t)d.h_small[1] != 0)
+			rc[g] = SNAPPY_INVALID_INPUT;
+		cudaEventElapsedTime(&tm[g].copy_in, d.ev[0], d.ev[1]);
+		cudaEventElapsedTime(&tm[g].run, d.ev[1], d.ev[2]);
+		cudaEventElapsedTime(&tm[g].copy_out, d.ev[2], d.ev[3]);
+	});
+	for (int g = 0; g < ng; g++) {
+		if (rc[g] != SNAPPY_OK)
+			return (snappy_status)rc[g];
+		runtime->d_alloc = std::max(runtime->d_alloc, tm[g].alloc);
+		runtime->copy_in = std::max(runtime->copy_in, tm[g].copy_in * 1e-3);
+		runtime->run = std::max(runtime->run, tm[g].run * 1e-3);
+		runtime->copy_out = std::max(runtime->copy_out, tm[g].copy_out * 1e-3);
+	}
+	input->curr = const_cast<uint8_t *>(end);
+	output->curr = output->buffer + out_len;
+	return SNAPPY_OK;
+}
+
+// the reference's names
+extern "C" snappy_status snappy_compress_dpu(struct host_buffer_context *input, struct host_buffer_context *output, uint32_t block_size,
+                                             struct program_runtime *runtime)
+{
+	return snappy_compress_gpu(input, output, block_size, runtime);
+}
+
+extern "C" snappy_status snappy_decompress_dpu(struct host_buffer_context *input, struct host_buffer_context *output,
+                                               struct program_runtime *runtime)
+{
+	return snappy_decompress_gpu(input, output, runtime);
+}

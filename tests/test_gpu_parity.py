@@ -1,0 +1,226 @@
+"""GPU parity tests (run on the B200 box with -m gpu).  Every call goes through the C ABI
+(ctypes -> libpim_snappy.so); the oracle is only the checker."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import edge_inputs
+
+pytestmark = pytest.mark.gpu
+
+IN_DOMAIN = [4096, 8192, 16384, 32768, 65535]
+
+
+def _roundtrip_check(P, oracle, name, data, bs, ref_decoder_ok=True):
+    want = oracle.compress(data, bs)
+    got = P.compress(data, bs)
+    assert got.size == want.size and np.array_equal(got, want), f"compress mismatch {name} bs={bs}: {got.size} vs {want.size}, first diff {np.flatnonzero(got[:min(got.size, want.size)] != want[:min(got.size, want.size)])[:4]}"
+    back = P.decompress(want)
+    assert back.size == data.size and np.array_equal(back, data), f"decompress mismatch {name} bs={bs}, first diff {np.flatnonzero(back[:data.size] != data[:back.size])[:4]}"
+    if ref_decoder_ok:
+        rc, o = oracle.decompress(got)
+        assert rc == 0 and np.array_equal(o, data)
+
+
+def test_golden_fixtures(P, oracle, golden):
+    # the reference's `make test_dpu` (snappy/Makefile:58-60) + the implicit compression KATs
+    for name, (txt, sn) in golden.items():
+        out = P.decompress(sn)
+        assert np.array_equal(out, txt), name
+        comp = P.compress(txt, 32768)
+        assert np.array_equal(comp, sn), name
+
+
+def test_edge_cases(P, oracle):
+    for name, data in edge_inputs().items():
+        for bs in (1000, 32768, 65535):
+            _roundtrip_check(P, oracle, name, data, bs)
+
+
+def test_tiny_blocks(P, oracle):
+    data = edge_inputs()["text1000"]
+    for bs in (1, 2, 3, 14, 15, 16, 17, 60, 61, 64, 100, 255, 257):
+        _roundtrip_check(P, oracle, "text1000", data, bs)
+
+
+def test_block_size_sweep_corpus(P, oracle, golden):
+    for name in ("terror2", "plrabn12", "world192", "xml"):
+        txt = golden[name][0]
+        for bs in IN_DOMAIN + [1000, 20000]:
+            _roundtrip_check(P, oracle, name, txt, bs)
+
+
+def test_block_65536(P, oracle, golden):
+    # row Q: compress-bytes parity + GPU round trip vs the original (the REFERENCE decoder breaks on
+    # all-literal 64 KiB blocks, so it is not consulted here)
+    for name, data in (("world192", golden["world192"][0]), ("rand", np.random.default_rng(5).integers(0, 256, 300000, dtype=np.uint8)),
+                       ("mix", None)):
+        if data is None:
+            data = P.synth_host(P.SYNTH_MIX, 0x64, 3 << 20)
+        _roundtrip_check(P, oracle, name, data, 65536, ref_decoder_ok=False)
+
+
+def test_synthetic_kinds(P, oracle):
+    for kind in (P.SYNTH_TEXT, P.SYNTH_RANDOM, P.SYNTH_MIX, P.SYNTH_BIN):
+        data = P.synth_host(kind, 0x5BA0 + kind, (5 << 20) + 12345)
+        for bs in (4096, 32768, 65535):
+            _roundtrip_check(P, oracle, f"synth{kind}", data, bs)
+
+
+def test_config2_dickens_standin(P, oracle, golden):
+    # BASELINE.json config 2 (dickens.txt is absent upstream): SYN-TEXT-10M and CORPUS-10M, 32 KB blocks
+    n = 10192446
+    _roundtrip_check(P, oracle, "SYN-TEXT-10M", P.synth_host(P.SYNTH_TEXT, 0xD1C0, n), 32768)
+    parts = np.concatenate([golden[k][0] for k in ("world192", "plrabn12", "terror2", "xml")])
+    corpus = np.tile(parts, n // parts.size + 1)[:n]
+    _roundtrip_check(P, oracle, "CORPUS-10M", corpus, 32768)
+
+
+def test_config3_block_sweep_standins(P, oracle):
+    # BASELINE.json config 3 stand-ins (mozilla / spamfile absent): SYN-BIN-51M, SYN-TEXT-84M
+    bin51 = P.synth_host(P.SYNTH_BIN, 0x0B1A, 51220480)
+    txt84 = P.synth_host(P.SYNTH_TEXT, 0x5BA0, 84217482)
+    for bs in IN_DOMAIN:
+        _roundtrip_check(P, oracle, "SYN-BIN-51M", bin51, bs)
+    for bs in (4096, 32768):
+        _roundtrip_check(P, oracle, "SYN-TEXT-84M", txt84, bs)
+    for bs in (131072, 1 << 20):  # outside the reference's valid domain (row Q): rejected, not mis-compressed
+        with pytest.raises(P.SnappyError) as e:
+            P.compress(bin51[: 1 << 21], bs)
+        assert e.value.status == P.SNAPPY_BUFFER_TOO_SMALL
+
+
+def test_copy4_and_long_literal_elements(P, oracle):
+    # the compressor never emits COPY_4 or 4-byte literal lengths, the decoder must accept them
+    # (snappy_decompress.c:118-133,278-283; :64-74)
+    lit = np.arange(200, dtype=np.uint8)
+    body = bytes([60 << 2, 199]) + lit.tobytes()                 # literal, 1 extra length byte
+    body += bytes([0x03 | (9 << 2)]) + (150).to_bytes(4, "little")  # COPY_4 len 10 offset 150
+    body += bytes([63 << 2]) + (49).to_bytes(4, "little") + bytes(range(50))  # literal, 4 extra length bytes
+    body += bytes([0x02 | (63 << 2)]) + (1).to_bytes(2, "little")  # COPY_2 len 64 offset 1 (overlap)
+    dlen = 200 + 10 + 50 + 64
+    stream = np.frombuffer(bytes([dlen & 0x7F | 0x80, dlen >> 7]) + b"\x80\x80\x02" + len(body).to_bytes(4, "little") + body, dtype=np.uint8)
+    rc, want = oracle.decompress_strict(stream)
+    assert rc == 0 and want.size == dlen
+    assert np.array_equal(P.decompress(stream), want)
+
+
+def test_malformed_streams(P, oracle):
+    good = oracle.compress(edge_inputs()["text1000"], 256)
+    with pytest.raises(P.SnappyError) as e:  # five continuation bytes in the length varint
+        bad = good.copy(); bad[0:5] = 0xFF
+        P.decompress(bad)
+    assert e.value.status == P.SNAPPY_INVALID_INPUT
+    with pytest.raises(P.SnappyError) as e:  # dlength > output->max (snappy_decompress.c:201-204)
+        P.decompress(good, max_len=10)
+    assert e.value.status == P.SNAPPY_BUFFER_TOO_SMALL
+    hdr = b"\x08\x80\x80\x02"
+    cases = {
+        "copy before start": hdr + b"\x03\x00\x00\x00" + bytes([0x01 | (4 << 2), 0x09, 0x00]),
+        "zero offset": hdr + b"\x06\x00\x00\x00" + bytes([3 << 2]) + b"abcd" + bytes([0x01, 0x00]),
+        "literal overruns input": hdr + b"\x03\x00\x00\x00" + bytes([7 << 2]) + b"ab",
+        "output too long": hdr + b"\x0c\x00\x00\x00" + bytes([10 << 2]) + b"abcdefghijk",
+        "output too short": hdr + b"\x04\x00\x00\x00" + bytes([2 << 2]) + b"abc",
+        "truncated block": hdr + b"\x40\x00\x00\x00" + bytes([2 << 2]) + b"abc",
+        "truncated copy2": hdr + b"\x07\x00\x00\x00" + bytes([4 << 2]) + b"abcde" + bytes([0x02 | (2 << 2)]),
+    }
+    for name, raw in cases.items():
+        s = np.frombuffer(raw, dtype=np.uint8)
+        assert oracle.decompress_strict(s)[0] == 1, name
+        with pytest.raises(P.SnappyError) as e:
+            P.decompress(s)
+        assert e.value.status == P.SNAPPY_INVALID_INPUT, name
+    # random garbage bodies must be rejected or decoded without faulting, never hang
+    rng = np.random.default_rng(99)
+    for i in range(20):
+        body = rng.integers(0, 256, 5000, dtype=np.uint8).tobytes()
+        s = np.frombuffer(b"\xa0\x9c\x01" + b"\x80\x80\x02" + len(body).to_bytes(4, "little") + body, dtype=np.uint8)
+        try:
+            out = P.decompress(s)
+            rc, want = oracle.decompress_strict(s)
+            assert rc == 0 and np.array_equal(out, want)
+        except P.SnappyError as e:
+            assert e.status == P.SNAPPY_INVALID_INPUT and oracle.decompress_strict(s)[0] == 1
+    assert np.array_equal(P.decompress(good), edge_inputs()["text1000"])  # the device is still healthy
+
+
+def test_device_resident_api_and_generators(P, oracle):
+    import torch
+    dev = torch.device("cuda:0")
+    n, bs = (8 << 20) + 333, 32768
+    host = P.synth_host(P.SYNTH_MIX, 0xFEED, n)
+    d_in = torch.empty(n, dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    P.synth_device(P.SYNTH_MIX, 0xFEED, d_in.data_ptr(), n, st)
+    assert np.array_equal(d_in.cpu().numpy(), host)  # host and device generators agree bit for bit
+    L = P.lib()
+    nb = L.pim_snappy_num_blocks(n, bs)
+    scratch = torch.empty(L.pim_snappy_compress_scratch_bytes(n, bs), dtype=torch.uint8, device=dev)
+    d_out = torch.empty(L.pim_snappy_compress_bound(n, bs), dtype=torch.uint8, device=dev)
+    d_off = torch.empty(nb + 1, dtype=torch.int64, device=dev)
+    P.compress_device(d_in.data_ptr(), n, bs, scratch.data_ptr(), scratch.numel(), d_out.data_ptr(), d_off.data_ptr(), st)
+    torch.cuda.synchronize()
+    off = d_off.cpu().numpy().astype(np.uint64)
+    want = oracle.compress(host, bs)
+    hlen, dlen, bs2, woff = P.block_offsets(want)
+    assert np.array_equal(off, woff)
+    assert np.array_equal(d_out[: int(off[-1])].cpu().numpy(), want[hlen:])
+    d_back = torch.zeros(n, dtype=torch.uint8, device=dev)
+    d_status = torch.ones(1, dtype=torch.int32, device=dev)
+    P.decompress_device(d_out.data_ptr(), d_off.data_ptr(), nb, bs, n, d_back.data_ptr(), d_status.data_ptr(), st)
+    torch.cuda.synchronize()
+    assert int(d_status.item()) == 0 and torch.equal(d_back, d_in)
+
+
+def test_large_roundtrip_properties(P):
+    """BASELINE-size property test (no oracle): 1 GiB mixed stream, compress -> decompress == input,
+    block offsets consistent, result independent of how the work is repeated (determinism)."""
+    import torch
+    dev = torch.device("cuda:0")
+    n, bs = 1 << 30, 32768
+    L = P.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    d_in = torch.empty(n, dtype=torch.uint8, device=dev)
+    P.synth_device(P.SYNTH_MIX, 0x64000000, d_in.data_ptr(), n, st)
+    nb = L.pim_snappy_num_blocks(n, bs)
+    scratch = torch.empty(L.pim_snappy_compress_scratch_bytes(n, bs), dtype=torch.uint8, device=dev)
+    d_out = torch.empty(L.pim_snappy_compress_bound(n, bs), dtype=torch.uint8, device=dev)
+    d_off = torch.empty(nb + 1, dtype=torch.int64, device=dev)
+    P.compress_device(d_in.data_ptr(), n, bs, scratch.data_ptr(), scratch.numel(), d_out.data_ptr(), d_off.data_ptr(), st)
+    torch.cuda.synchronize()
+    total = int(d_off[-1].item())
+    assert 0.70 * n < total < 0.85 * n  # SYN-MIX compresses to ~0.77
+    sizes = (d_off[1:] - d_off[:-1])
+    assert int(sizes.min().item()) > 4 and int(sizes.max().item()) <= bs + bs // 6 + 36
+    chk1 = int(d_out[:total].to(torch.int64).sum().item())
+    d_back = torch.zeros(n, dtype=torch.uint8, device=dev)
+    d_status = torch.ones(1, dtype=torch.int32, device=dev)
+    P.decompress_device(d_out.data_ptr(), d_off.data_ptr(), nb, bs, n, d_back.data_ptr(), d_status.data_ptr(), st)
+    torch.cuda.synchronize()
+    assert int(d_status.item()) == 0 and torch.equal(d_back, d_in)
+    d_out.zero_()
+    P.compress_device(d_in.data_ptr(), n, bs, scratch.data_ptr(), scratch.numel(), d_out.data_ptr(), d_off.data_ptr(), st)
+    torch.cuda.synchronize()
+    assert int(d_off[-1].item()) == total and int(d_out[:total].to(torch.int64).sum().item()) == chk1
+
+
+def test_cli_matches_reference_contract(P, golden, tmp_path):
+    # same lines the reference CLI prints (dpu_snappy.c:152,159,212-227), same round trip as `make test`
+    cli = os.path.join(os.path.dirname(P.LIB_PATH), "dpu_snappy")
+    txt, sn = golden["terror2"]
+    src, comp, back = tmp_path / "t.txt", tmp_path / "t.snappy", tmp_path / "t.out"
+    src.write_bytes(txt.tobytes())
+    r = subprocess.run([cli, "-d", "-c", "-b", "32768", "-i", str(src), "-o", str(comp)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert comp.read_bytes() == sn.tobytes()
+    lines = r.stdout.splitlines()
+    assert lines[0] == f"Using input file {src}" and lines[1] == f"Using output file {comp}"
+    assert lines[2] == f"Compressed {sn.size} bytes to: {comp}" and lines[3].startswith("Compression ratio: 0.50")
+    assert [l.split(":")[0] for l in lines[4:]] == ["Pre-processing time", "Alloc time", "Load time", "Copy in time", "Host time", "Copy out time", "Free time"]
+    r = subprocess.run([cli, "-d", "-i", str(comp), "-o", str(back)], capture_output=True, text=True)
+    assert r.returncode == 0 and back.read_bytes() == txt.tobytes()
+    assert f"Decompressed {txt.size} bytes to: {back}" in r.stdout
+    assert subprocess.run([cli], capture_output=True).returncode == 255      # missing -i  -> -1
+    assert subprocess.run([cli, "-x"], capture_output=True).returncode == 254  # bad option -> -2
