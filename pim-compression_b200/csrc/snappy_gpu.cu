@@ -437,8 +437,18 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 	for (int g = 0; g < ng; g++)
 		at[g + 1] = at[g] + total[g];
 	if (at[ng] > cap) {
-		fprintf(stderr, "pim_snappy: compressed size %llu exceeds the output buffer (%zu)\n", (unsigned long long)at[ng], cap);
-		return SNAPPY_BUFFER_TOO_SMALL;
+		// Only tiny block sizes get here (4 header bytes per block dominate).  A buffer that
+		// setup_compression() allocated is ours to replace; a foreign one is not.
+		if (owned_capacity(output->buffer) == 0 || at[ng] > output->max) {
+			fprintf(stderr, "pim_snappy: compressed size %llu exceeds the output buffer (%zu)\n", (unsigned long long)at[ng], cap);
+			return SNAPPY_BUFFER_TOO_SMALL;
+		}
+		uint8_t *bigger = static_cast<uint8_t *>(pim_snappy_host_alloc(at[ng] + 64));
+		if (!bigger)
+			return SNAPPY_BUFFER_TOO_SMALL;
+		memcpy(bigger, output->buffer, hlen);
+		pim_snappy_host_free(output->buffer);
+		output->buffer = bigger;
 	}
 
 	// phase 2: D2H straight into the final position
