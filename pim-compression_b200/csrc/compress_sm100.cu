@@ -389,6 +389,7 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 	if (dev < 64 && !configured_for[dev]) {
 		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
 		                                  (int)compress_smem_bytes(PIM_SNAPPY_MAX_BLOCK_SIZE)));
+		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
 		configured_for[dev] = 1;
 	}
 	prof_begin(0, st);

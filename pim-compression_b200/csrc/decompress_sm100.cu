@@ -34,7 +34,9 @@ constexpr uint32_t SM_NREC = 0;       // u32[2]
 constexpr uint32_t SM_LAST = 8;       // u32[2]
 constexpr uint32_t SM_ERR = 16;       // u32
 constexpr uint32_t SM_SEGBASE = 64;   // u32[2][32]
-constexpr uint32_t SM_STAGE = 320;    // u8[2][STAGE_BYTES]
+constexpr uint32_t SM_LUT = 320;      // u8[256]: compressed footprint of an element by tag byte (0 = long literal)
+constexpr uint32_t SM_EX = 576;       // u16[32][32]: parser's exit table, [offset in segment][segment]
+constexpr uint32_t SM_STAGE = SM_EX + 2048; // u8[2][STAGE_BYTES]
 constexpr uint32_t SM_REC = SM_STAGE + 2 * STAGE_BYTES; // uint2[2][MAX_REC]
 constexpr uint32_t SM_TILE = SM_REC + 2 * MAX_REC * 8;
 static_assert(SM_REC % 16 == 0 && SM_TILE % 16 == 0, "alignment");
@@ -53,75 +55,180 @@ __host__ __device__ inline uint32_t decompress_smem_bytes(uint32_t block_size)
 }
 
 // ---------------------------------------------------------------------------
-// Parser, serial form: lane 0 walks the tags of one chunk.
-// Returns the compressed position after the chunk's last element.
+// Element decode (snappy_decompress.c:242-283, :64-133).  `so` = shared-memory offset of the
+// tag byte, `cp` = its position in the block's compressed bytes.  Returns false if malformed.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t parse_chunk_serial(uint8_t *sm, int b, uint32_t stage_off /* smem offset of compressed byte `cs` */,
-                                                       uint32_t cs, uint32_t cp, uint32_t csize, uint32_t out_base, uint32_t out_size,
-                                                       uint32_t *out_total)
+struct Element {
+	uint32_t len;  // bytes produced
+	uint32_t foot; // compressed bytes occupied
+	uint32_t type; // T_*
+	uint32_t src;  // see T_*
+};
+
+__device__ __forceinline__ bool decode_element(const uint8_t *sm, uint32_t so, uint32_t cp, uint32_t csize, uint32_t staged_end, Element &e)
 {
-	uint2 *rec = reinterpret_cast<uint2 *>(sm + SM_REC) + b * MAX_REC;
-	uint32_t n = 0, local = 0;
-	bool bad = false;
-	const uint32_t staged_end = cs + CHUNK + TAIL;
-	while (cp < cs + CHUNK && cp < csize) {
-		const uint32_t so = stage_off + (cp - cs);
-		const uint32_t v = lds32_unaligned(sm, so); // tag + next three bytes
-		const uint32_t tag = v & 0xFF;
-		const uint32_t kind = tag & 3;
-		uint32_t len, foot, src, type;
-		if (kind == 0) {
-			const uint32_t n6 = tag >> 2;
-			uint32_t hdr = 1;
-			if (n6 < 60) {
-				len = n6 + 1;
-			} else {
-				const uint32_t nb = n6 - 59;
-				hdr = 1 + nb;
-				if (cp + hdr > csize) { bad = true; break; }
-				uint32_t lm1 = (nb == 4) ? ((v >> 8) | (uint32_t(sm[so + 4]) << 24)) : ((v >> 8) & ((1u << (8 * nb)) - 1));
-				if (lm1 >= 65536u) { bad = true; break; }
-				len = lm1 + 1;
-			}
-			if (len > csize - cp - hdr) { bad = true; break; }
-			foot = hdr + len;
-			if (len <= SHORT_LEN && cp + foot <= staged_end) {
-				type = T_LIT_SMEM;
-				src = so + hdr;
-			} else {
-				type = T_LIT_GMEM;
-				src = cp + hdr;
-			}
+	const uint32_t v = lds32_unaligned(sm, so); // tag + next three bytes
+	const uint32_t tag = v & 0xFF;
+	const uint32_t kind = tag & 3;
+	if (kind == 0) {
+		const uint32_t n6 = tag >> 2;
+		uint32_t hdr = 1;
+		if (n6 < 60) {
+			e.len = n6 + 1;
 		} else {
-			type = T_COPY;
-			if (kind == 1) {
-				foot = 2;
-				len = ((tag >> 2) & 7) + 4;
-				src = ((tag >> 5) << 8) | ((v >> 8) & 0xFF);
-			} else if (kind == 2) {
-				foot = 3;
-				len = (tag >> 2) + 1;
-				src = (v >> 8) & 0xFFFF;
-			} else {
-				foot = 5;
-				len = (tag >> 2) + 1;
-				src = (v >> 8) | (uint32_t(sm[so + 4]) << 24);
-				if (src > 65535u) { bad = true; break; }
-			}
-			if (cp + foot > csize) { bad = true; break; }
+			const uint32_t nb = n6 - 59;
+			hdr = 1 + nb;
+			if (cp + hdr > csize)
+				return false;
+			const uint32_t lm1 = (nb == 4) ? ((v >> 8) | (uint32_t(sm[so + 4]) << 24)) : ((v >> 8) & ((1u << (8 * nb)) - 1));
+			if (lm1 >= 65536u)
+				return false;
+			e.len = lm1 + 1;
 		}
-		if (out_base + local + len > out_size) { bad = true; break; }
-		rec[n] = make_uint2(local | ((len - 1) << 16), (type << 30) | src);
-		local += len;
-		n++;
-		cp += foot;
+		if (e.len > csize - cp - hdr)
+			return false;
+		e.foot = hdr + e.len;
+		if (e.len <= SHORT_LEN && cp + e.foot <= staged_end) {
+			e.type = T_LIT_SMEM;
+			e.src = so + hdr;
+		} else {
+			e.type = T_LIT_GMEM;
+			e.src = cp + hdr;
+		}
+		return true;
 	}
-	reinterpret_cast<uint32_t *>(sm + SM_SEGBASE)[b * 32] = out_base;
-	reinterpret_cast<uint32_t *>(sm + SM_NREC)[b] = n;
-	if (bad)
+	e.type = T_COPY;
+	if (kind == 1) {
+		e.foot = 2;
+		e.len = ((tag >> 2) & 7) + 4;
+		e.src = ((tag >> 5) << 8) | ((v >> 8) & 0xFF);
+	} else if (kind == 2) {
+		e.foot = 3;
+		e.len = (tag >> 2) + 1;
+		e.src = (v >> 8) & 0xFFFF;
+	} else {
+		e.foot = 5;
+		e.len = (tag >> 2) + 1;
+		e.src = (v >> 8) | (uint32_t(sm[so + 4]) << 24);
+		if (e.src > 65535u)
+			return false;
+	}
+	return cp + e.foot <= csize;
+}
+
+// footprint of a long literal (tag>>2 >= 60); BIG_FOOT if malformed.  Must agree with decode_element.
+constexpr uint32_t BIG_FOOT = 0x100000u;
+__device__ __forceinline__ uint32_t long_literal_foot(const uint8_t *sm, uint32_t so, uint32_t cp, uint32_t csize)
+{
+	const uint32_t v = lds32_unaligned(sm, so);
+	const uint32_t nb = ((v & 0xFF) >> 2) - 59;
+	if (cp + 1 + nb > csize)
+		return BIG_FOOT;
+	const uint32_t lm1 = (nb == 4) ? ((v >> 8) | (uint32_t(sm[so + 4]) << 24)) : ((v >> 8) & ((1u << (8 * nb)) - 1));
+	return lm1 >= 65536u ? BIG_FOOT : 2 + nb + lm1;
+}
+
+__device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v, int lane)
+{
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		const uint32_t t = __shfl_up_sync(FULL, v, d);
+		if (lane >= d)
+			v += t;
+	}
+	return v;
+}
+
+// ---------------------------------------------------------------------------
+// Parser: the tag chain of a 1 KB chunk is inherently serial (an element's length says where
+// the next tag is), so the warp resolves it in three data-parallel phases:
+//   1. lane s owns compressed bytes [32s, 32s+32) of the chunk.  Walking its bytes backwards
+//      it fills an "exit table": for EVERY byte offset j, where a chain entering the segment
+//      at j leaves it, and how many elements it passes (a dynamic program over
+//      next(j) = j + footprint(j), with footprints from a 256-entry table by tag byte);
+//   2. the true chain is then 32 table look-ups, one per segment, starting from the known
+//      entry position of the chunk;
+//   3. every lane decodes the elements of its own segment from its true entry and writes
+//      their records; prefix sums over the lanes give record slots and output positions.
+// Returns the compressed position of the first element of the next chunk (0xFFFFFFFF on a
+// malformed element).
+// ---------------------------------------------------------------------------
+constexpr uint32_t EX_FAR = 0x7FFu; // exit "beyond anything this chunk cares about"
+
+__device__ __forceinline__ uint32_t parse_chunk_parallel(uint8_t *sm, int b, uint32_t stage_off, uint32_t cs, uint32_t cp, uint32_t csize,
+                                                         uint32_t out_base, uint32_t *out_total, int lane)
+{
+	uint16_t *ex = reinterpret_cast<uint16_t *>(sm + SM_EX);
+	const uint8_t *lut = sm + SM_LUT;
+	const uint32_t seg_so = stage_off + 32u * lane; // smem offset of my segment
+	const uint32_t seg_cp = cs + 32u * lane;        // compressed position of my segment
+
+	// ---- phase 1: exit table -------------------------------------------------------------
+#pragma unroll 4
+	for (int j = 31; j >= 0; j--) {
+		uint32_t v = EX_FAR; // positions past the end of the block: no element, exit far
+		if (seg_cp + j < csize) {
+			uint32_t f = lut[sm[seg_so + j]];
+			if (f == 0)
+				f = long_literal_foot(sm, seg_so + j, seg_cp + j, csize);
+			const uint32_t n = j + f;
+			if (n < 32)
+				v = ex[n * 32 + lane] + (1u << 11); // same exit, one more element
+			else
+				v = min(n, EX_FAR) | (1u << 11);
+		}
+		ex[j * 32 + lane] = (uint16_t)v;
+	}
+	__syncwarp();
+
+	// ---- phase 2: follow the true chain across the segments ----------------------------------
+	uint32_t x = cp - cs; // entry, relative to the chunk
+	const uint32_t csz = csize - cs;
+	uint32_t my_x = 0, my_cnt = 0;
+	for (int s = 0; s < 32; s++) {
+		if (x >= 1024u || x >= csz)
+			break;
+		if (x < 32u * s + 32u) {
+			const uint32_t w = ex[(x - 32u * s) * 32 + s];
+			if (lane == s) {
+				my_x = x;
+				my_cnt = w >> 11;
+			}
+			const uint32_t e = w & 0x7FFu;
+			x = e == EX_FAR ? 0xFFFFFFu : 32u * s + e;
+		}
+	}
+
+	// ---- phase 3: decode my segment's elements into records ----------------------------------
+	const uint32_t cnt_incl = warp_inclusive_scan(my_cnt, lane);
+	const uint32_t nrec = __shfl_sync(FULL, cnt_incl, 31);
+	uint2 *rec = reinterpret_cast<uint2 *>(sm + SM_REC) + b * MAX_REC + (cnt_incl - my_cnt);
+	const uint32_t staged_end = cs + CHUNK + TAIL;
+	uint32_t p = cs + my_x, local = 0;
+	bool bad = false;
+	const uint32_t max_cnt = __reduce_max_sync(FULL, my_cnt);
+	for (uint32_t k = 0; k < max_cnt; k++) {
+		if (k < my_cnt && !bad) {
+			Element e;
+			if (!decode_element(sm, stage_off + (p - cs), p, csize, staged_end, e) || local > 0xFFFFu) {
+				bad = true;
+				e.len = 1; e.foot = 1; e.type = T_LIT_SMEM; e.src = 0;
+			}
+			rec[k] = make_uint2((local & 0xFFFFu) | ((e.len - 1) << 16), (e.type << 30) | ((uint32_t)lane << 24) | e.src);
+			local += e.len;
+			p += e.foot;
+		}
+	}
+	const uint32_t out_incl = warp_inclusive_scan(local, lane);
+	reinterpret_cast<uint32_t *>(sm + SM_SEGBASE)[b * 32 + lane] = out_base + out_incl - local;
+	*out_total = out_base + __shfl_sync(FULL, out_incl, 31);
+	if (lane == 0)
+		reinterpret_cast<uint32_t *>(sm + SM_NREC)[b] = nrec;
+	const bool any_bad = __any_sync(FULL, bad);
+	if (any_bad && lane == 0)
 		*reinterpret_cast<volatile uint32_t *>(sm + SM_ERR) = 1;
-	*out_total = out_base + local;
-	return bad ? 0xFFFFFFFFu : cp;
+	const uint32_t next_cp = __reduce_max_sync(FULL, my_cnt ? p : 0u);
+	return any_bad ? 0xFFFFFFFFu : next_cp;
 }
 
 // ---------------------------------------------------------------------------
@@ -222,7 +329,7 @@ __device__ __forceinline__ void copier_batch(uint8_t *sm, const uint8_t *gcomp, 
 // ---------------------------------------------------------------------------
 // Kernel: grid = number of blocks, 64 threads.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) snappy_decompress_kernel(const uint8_t *__restrict__ comp, const uint64_t *__restrict__ block_off,
+__global__ void __launch_bounds__(64, 8) snappy_decompress_kernel(const uint8_t *__restrict__ comp, const uint64_t *__restrict__ block_off,
                                                                uint32_t block_size, uint64_t out_len, uint8_t *__restrict__ out,
                                                                uint32_t *__restrict__ status)
 {
@@ -237,8 +344,11 @@ __global__ void __launch_bounds__(64) snappy_decompress_kernel(const uint8_t *__
 	uint8_t *gdst = out + out_off;
 	const uint32_t tile0 = SM_TILE + (uint32_t)(reinterpret_cast<uintptr_t>(gdst) & 15u);
 
-	if (threadIdx.x == 0) {
+	if (threadIdx.x == 0)
 		*reinterpret_cast<uint32_t *>(sm + SM_ERR) = 0;
+	for (uint32_t t = threadIdx.x; t < 256; t += 64) {
+		const uint32_t kind = t & 3, n6 = t >> 2;
+		sm[SM_LUT + t] = (uint8_t)(kind == 0 ? (n6 < 60 ? n6 + 2 : 0) : (kind == 1 ? 2 : (kind == 2 ? 3 : 5)));
 	}
 	__syncthreads();
 
@@ -271,10 +381,8 @@ __global__ void __launch_bounds__(64) snappy_decompress_kernel(const uint8_t *__
 			cp_async_wait<0>();
 			__syncwarp();
 			uint32_t total = 0;
-			if (lane == 0)
-				cp = parse_chunk_serial(sm, b, stage_off, cs, cp, csize, out_base, out_size, &total);
-			cp = __shfl_sync(FULL, cp, 0);
-			out_base = __shfl_sync(FULL, total, 0);
+			cp = parse_chunk_parallel(sm, b, stage_off, cs, cp, csize, out_base, &total, lane);
+			out_base = total;
 			bool last = cp >= csize; // also true for the error marker
 			if (last && lane == 0) {
 				if (cp != csize || out_base != out_size)
@@ -354,6 +462,7 @@ extern "C" snappy_status pim_snappy_decompress_device(const uint8_t *d_comp, con
 	if (dev < 64 && configured_for[dev] < (int)smem) {
 		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
 		                                  (int)decompress_smem_bytes(PIM_SNAPPY_MAX_BLOCK_SIZE)));
+		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
 		configured_for[dev] = (int)decompress_smem_bytes(PIM_SNAPPY_MAX_BLOCK_SIZE);
 	}
 	prof_begin(3, st);
