@@ -222,9 +222,11 @@ __device__ __forceinline__ uint32_t parse_chunk_parallel(uint8_t *sm, int b, uin
 	const uint32_t out_incl = warp_inclusive_scan(local, lane);
 	reinterpret_cast<uint32_t *>(sm + SM_SEGBASE)[b * 32 + lane] = out_base + out_incl - local;
 	*out_total = out_base + __shfl_sync(FULL, out_incl, 31);
-	if (lane == 0)
-		reinterpret_cast<uint32_t *>(sm + SM_NREC)[b] = nrec;
+	// A malformed element leaves the rest of its lane's record slots unwritten (stale): the
+	// batch is then dropped as a whole -- the block is reported invalid anyway.
 	const bool any_bad = __any_sync(FULL, bad);
+	if (lane == 0)
+		reinterpret_cast<uint32_t *>(sm + SM_NREC)[b] = any_bad ? 0u : nrec;
 	if (any_bad && lane == 0)
 		*reinterpret_cast<volatile uint32_t *>(sm + SM_ERR) = 1;
 	const uint32_t next_cp = __reduce_max_sync(FULL, my_cnt ? p : 0u);
@@ -383,6 +385,11 @@ __global__ void __launch_bounds__(64, 8) snappy_decompress_kernel(const uint8_t 
 			uint32_t total = 0;
 			cp = parse_chunk_parallel(sm, b, stage_off, cs, cp, csize, out_base, &total, lane);
 			out_base = total;
+			if (out_base > out_size) { // decodes to more than the block holds: stop before positions can wrap
+				if (lane == 0)
+					*reinterpret_cast<volatile uint32_t *>(sm + SM_ERR) = 1;
+				cp = 0xFFFFFFFFu;
+			}
 			bool last = cp >= csize; // also true for the error marker
 			if (last && lane == 0) {
 				if (cp != csize || out_base != out_size)
