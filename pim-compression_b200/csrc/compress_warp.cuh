@@ -1,0 +1,550 @@
+// Per-warp Snappy block compressor: one warp compresses one input block and reproduces, bit for
+// bit, the reference's HOST compressor compress_block (snappy/snappy_compress.c:284-413): same
+// hash (:161-166), same skip schedule (:333-348), same order of table updates (:391-397), same
+// element encodings (:202-272).
+//
+// The reference loop alternates   step 1: probe positions until a 4-byte match is found
+//                                 step 2: emit the pending literal
+//                                 step 3: emit the copy, insert ip-1, probe ip; repeat while it matches.
+// All three are driven here by ONE kind of pass over 32 lanes:
+//
+//   * "ic" layout (after a match that ended at q):  lane 0 = insert-only position q-1 (:388-389),
+//     lane 1 = the step-3 continuation probe at q (:391-394), lane 2+i = step-1 probe i at q+1+i
+//     (the first 32 probes of step 1 have stride 1, :333-340);
+//   * "probe" layout (block start, or a step 1 that needs more than the ic pass covers):
+//     lane i = step-1 probe k0+i at its position in the reference's schedule (stride (32+k)>>5).
+//
+// Every lane loads the 16 bytes at its position, hashes the first four, reads its table slot
+// and compares 16 bytes at the candidate, so a lane knows whether it hits AND its match length
+// up to 16 without another shared-memory round trip.  Table updates that earlier lanes of the
+// same pass would have made are forwarded with __match_any_sync (the candidate of a lane is the
+// closest lower lane with the same hash that is really inserted, else the table's entry).
+//
+// In a dense pass (all lanes at consecutive positions) the warp then resolves SEVERAL
+// (literal, copy) pairs without touching shared memory again: first hit lane f, match length m
+// -> the next pair's insert-only lane is f+m-1, its continuation probe f+m, its probes follow;
+// lanes inside the match are skipped (never inserted).  All literals and copy tags found that
+// way are written by one batched emission (prefix sums over ballot masks), and one table
+// update (last writer per slot wins) closes the pass.  Matches of 16 bytes or more are extended
+// by the whole warp (16 bytes per lane per step).
+//
+// This header is written against warp_prims.cuh so that the identical source also runs on the
+// host lock-step emulator (tests/emu) against the oracle.
+#pragma once
+
+#include "warp_prims.cuh"
+
+#ifdef PIM_WARP_EMU_STATS // emulator-only counters (tests/emu): passes, pairs, ... per run
+namespace pimsnappy { extern unsigned long cw_stats[8]; }
+#define CW_STAT(i) do { if (wp::lane() == 0) pimsnappy::cw_stats[i]++; } while (0)
+#else
+#define CW_STAT(i) do { } while (0)
+#endif
+
+namespace pimsnappy {
+
+constexpr uint32_t CW_MAX_TABLE = 16384; // snappy_compress.c:16-17
+constexpr uint32_t CW_MARGIN = 15;       // snappy_compress.c:299
+constexpr int CW_CHAIN_MAX = 24;         // a new pair is resolved in the same pass if its insert lane is <= this
+
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline uint32_t cw_table_entries(uint32_t n) // snappy_compress.c:139-146
+{
+	uint32_t ts = 256;
+	while (ts < CW_MAX_TABLE && ts < n)
+		ts <<= 1;
+	return ts;
+}
+
+struct CBlock {
+	const uint8_t *in; // input byte 0 (shared memory on the device); 24 readable bytes before/after [0, n)
+	uint16_t *table;   // zeroed, cw_table_entries(n) entries
+	int shift;         // 32 - log2(entries), snappy_compress.c:288
+	uint8_t *out;      // output slot: 4-byte size field + elements
+	uint32_t n;        // input bytes
+};
+
+namespace cw {
+
+// four / sixteen bytes at an arbitrary address (aligned word loads + funnel shifts)
+PW_FN uint32_t load32u(const uint8_t *p)
+{
+	const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+	const uint32_t *w = reinterpret_cast<const uint32_t *>(a & ~uintptr_t(3));
+	return wp::funnel_r(w[0], w[1], (uint32_t)(a & 3u) * 8u);
+}
+PW_FN void load128u(const uint8_t *p, uint32_t v[4])
+{
+	const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+	const uint32_t *w = reinterpret_cast<const uint32_t *>(a & ~uintptr_t(3));
+	const uint32_t sh = (uint32_t)(a & 3u) * 8u;
+	const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+	v[0] = wp::funnel_r(w0, w1, sh);
+	v[1] = wp::funnel_r(w1, w2, sh);
+	v[2] = wp::funnel_r(w2, w3, sh);
+	v[3] = wp::funnel_r(w3, w4, sh);
+}
+
+// number of equal leading bytes (0..16) of in[cand..] and the sixteen bytes `cur`
+PW_FN uint32_t common_prefix16(const uint8_t *in, uint32_t cand, const uint32_t cur[4])
+{
+	uint32_t cwd[4];
+	load128u(in + cand, cwd);
+	uint32_t m = 16;
+#pragma unroll
+	for (int w = 3; w >= 0; w--) {
+		const uint32_t d = cur[w] ^ cwd[w];
+		if (d)
+			m = 4u * w + ((uint32_t)(wp::ffs32(d) - 1) >> 3);
+	}
+	return m;
+}
+
+// lanes a..b inclusive (empty if b < a); 0 <= a, b <= 31
+PW_FN uint32_t lanes(int a, int b)
+{
+	return b < a ? 0u : (((2u << b) - 1u) & ~((1u << a) - 1u));
+}
+
+// snappy_compress.c:202-225 -- returns the new output cursor
+PW_FN uint32_t emit_literal(const CBlock &c, uint32_t o, uint32_t from, uint32_t len, int lane)
+{
+	const uint32_t n1 = len - 1;
+	uint32_t hdr;
+	if (n1 < 60) {
+		hdr = 1;
+		if (lane == 0)
+			c.out[o] = (uint8_t)(n1 << 2);
+	} else {
+		const uint32_t extra = n1 < 256 ? 1 : (n1 < 65536 ? 2 : 3); // n1 <= 65535 in the valid domain
+		hdr = 1 + extra;
+		if (lane == 0)
+			c.out[o] = (uint8_t)((59 + extra) << 2);
+		if (lane < (int)extra)
+			c.out[o + 1 + lane] = (uint8_t)(n1 >> (8 * lane));
+	}
+	uint8_t *dst = c.out + o + hdr;
+	const uint8_t *src = c.in + from;
+	uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u;
+	if (head > len)
+		head = len;
+	if ((uint32_t)lane < head)
+		dst[lane] = src[lane];
+	const uint32_t words = (len - head) >> 2;
+	uint32_t *d32 = reinterpret_cast<uint32_t *>(dst + head);
+	for (uint32_t i = lane; i < words; i += 32)
+		d32[i] = load32u(src + head + 4u * i);
+	const uint32_t done = head + 4u * words;
+	if (done + lane < len)
+		dst[done + lane] = src[done + lane];
+	return o + hdr + len;
+}
+
+// snappy_compress.c:234-245
+PW_FN uint32_t emit_copy_upto64(uint8_t *p, uint32_t off, uint32_t len)
+{
+	if (len < 12 && off < 2048) {
+		p[0] = (uint8_t)(1 + ((len - 4) << 2) + ((off >> 8) << 5));
+		p[1] = (uint8_t)off;
+		return 2;
+	}
+	p[0] = (uint8_t)(2 + ((len - 1) << 2));
+	p[1] = (uint8_t)off;
+	p[2] = (uint8_t)(off >> 8);
+	return 3;
+}
+
+// snappy_compress.c:254-272.  `while (len >= 68) emit 64` runs (len-4)/64 times.
+PW_FN uint32_t emit_copy(const CBlock &c, uint32_t o, uint32_t off, uint32_t len, int lane)
+{
+	const uint32_t n64 = len >= 68 ? (len - 4) / 64 : 0;
+	for (uint32_t t = lane; t < n64; t += 32) {
+		uint8_t *p = c.out + o + 3 * t;
+		p[0] = (uint8_t)(2 + (63 << 2));
+		p[1] = (uint8_t)off;
+		p[2] = (uint8_t)(off >> 8);
+	}
+	o += 3 * n64;
+	len -= 64 * n64;
+	const bool two = len > 64;
+	const uint32_t l1 = two ? 60 : len;
+	const uint32_t s1 = (l1 < 12 && off < 2048) ? 2 : 3;
+	uint32_t s2 = 0;
+	if (two) {
+		const uint32_t l2 = len - 60;
+		s2 = (l2 < 12 && off < 2048) ? 2 : 3;
+	}
+	if (lane == 0) {
+		emit_copy_upto64(c.out + o, off, l1);
+		if (two)
+			emit_copy_upto64(c.out + o + s1, off, len - 60);
+	}
+	return o + s1 + s2;
+}
+
+// snappy_compress.c:176-193: common prefix of in[a..] and in[b..], at most maxn bytes (b > a),
+// sixteen bytes per lane per step.
+PW_FN uint32_t match_length(const CBlock &c, uint32_t a, uint32_t b, uint32_t maxn, int lane)
+{
+	for (uint32_t base = 0;; base += 512) {
+		const uint32_t j = base + 16u * lane;
+		uint32_t cnt = 0; // equal bytes at the front of this lane's 16
+		if (j < maxn) {
+			uint32_t x[4];
+			load128u(c.in + b + j, x);
+			cnt = wp::umin(common_prefix16(c.in, a + j, x), maxn - j);
+		}
+		const uint32_t stop = wp::ballot(cnt < 16);
+		if (stop) {
+			const int l = wp::ffs32(stop) - 1;
+			return base + 16u * l + wp::shfl(cnt, l);
+		}
+	}
+}
+
+} // namespace cw
+
+namespace cw {
+
+// number of equal leading bytes (0..16) without FLO/BREV (those cost ~40 cycles on the chain)
+PW_FN uint32_t prefix16_fast(const uint8_t *in, uint32_t cand, const uint32_t cur[4])
+{
+	uint32_t cwd[4];
+	load128u(in + cand, cwd);
+	const uint32_t d0 = cur[0] ^ cwd[0], d1 = cur[1] ^ cwd[1], d2 = cur[2] ^ cwd[2], d3 = cur[3] ^ cwd[3];
+	const uint32_t d = d0 ? d0 : (d1 ? d1 : (d2 ? d2 : d3));
+	const uint32_t base = d0 ? 0u : (d1 ? 4u : (d2 ? 8u : (d3 ? 12u : 16u)));
+	const uint32_t inword = ((d & 0xFFu) == 0u) + ((d & 0xFFFFu) == 0u) + ((d & 0xFFFFFFu) == 0u); // d == 0 only when base == 16
+	return d ? base + inword : 16u;
+}
+
+// What a pass decided (uniform across the warp).
+struct PassOut {
+	uint32_t I;        // lanes whose positions are inserted into the table
+	uint32_t SK;       // lanes inside a match (never probed, never inserted)
+	uint32_t H;        // hit lanes
+	uint32_t L, LS;    // in-window literal bytes / first byte of each such literal
+	uint32_t satbit;   // hit lane whose match is >= 16 bytes (its copy is emitted by the extension path), else 0
+	uint32_t firstbit; // first hit lane of the pass
+	uint32_t lastbit;  // last hit lane
+	uint32_t insbit;   // insert lane of the pair the pass stopped in (0: none)
+	bool first;        // the pass stopped in its first pair
+	bool first_generic;// the first pair's literal started before the window
+	int outcome;       // 0: next pass in ic layout   1: keep probing   2: remainder   3: long match at satbit
+	bool redo;         // outcome 0 without a hit: redo the pair the pass stopped in
+};
+
+// Serial, always-exact resolution of the pairs of one pass: used when a lane's forwarded candidate
+// (a lower lane of the same pass with the same hash) turns out to lie inside a match.  cand / mlen
+// of a lane are re-evaluated whenever the set of skipped lanes changes its closest inserted lane.
+PW_FN void resolve_serial(const CBlock &c, PassOut &r, bool has_ic, bool dense, bool valid, uint32_t inval, uint32_t p, uint32_t tc,
+                          const uint32_t cur[4], uint32_t lowmask, uint32_t &cand, uint32_t &mlen, int lane)
+{
+	r.I = r.SK = r.H = r.L = r.LS = r.satbit = r.firstbit = r.lastbit = 0;
+	r.first = true;
+	r.first_generic = false;
+	r.redo = false;
+	int ins = has_ic ? 0 : -1;
+	int loaded = -2; // force an evaluation in the first round
+	for (;;) {
+		const int cont = ins + 1;
+		const uint32_t eff = lowmask & ~r.SK;
+		const int want = eff ? 31 - wp::clz32(eff) : -1;
+		if (want != loaded && valid) {
+			loaded = want;
+			cand = want < 0 ? tc : p - lane + want; // forwarding only happens in dense passes
+			mlen = common_prefix16(c.in, cand, cur);
+		}
+		const uint32_t hits = wp::ballot(valid && lane >= cont && mlen >= 4);
+		r.insbit = ins < 0 ? 0u : 1u << ins;
+		if (!hits) {
+			if (inval) {
+				r.outcome = 2;
+			} else if (r.first) {
+				r.I = 0xFFFFFFFFu;
+				r.outcome = 1;
+			} else {
+				r.outcome = 0;
+				r.redo = true;
+			}
+			return;
+		}
+		const int f = wp::ffs32(hits) - 1;
+		r.I |= lanes(ins < 0 ? 0 : ins, f);
+		const uint32_t mf = wp::shfl(mlen, f);
+		if (r.first && !has_ic) {
+			r.first_generic = true;
+		} else {
+			const uint32_t lit = lanes(cont, f - 1);
+			r.L |= lit;
+			if (lit)
+				r.LS |= 1u << cont;
+		}
+		r.H |= 1u << f;
+		r.lastbit = 1u << f;
+		if (r.first)
+			r.firstbit = 1u << f;
+		if (mf == 16) {
+			r.satbit = 1u << f;
+			r.outcome = 3;
+			return;
+		}
+		const int ins2 = f + (int)mf - 1;
+		const bool go = dense && ins2 <= CW_CHAIN_MAX && !((inval >> (ins2 + 1)) & 1u);
+		if (!go) {
+			r.outcome = 0;
+			return;
+		}
+		r.SK |= lanes(f + 1, ins2 - 1);
+		ins = ins2;
+		r.first = false;
+	}
+}
+
+} // namespace cw
+
+// Compress one block with the calling warp.  Returns the bytes written to c.out (4 + elements).
+PW_FN uint32_t compress_block_warp(const CBlock &c)
+{
+	using namespace cw;
+	const int lane = wp::lane();
+	const uint32_t mybit = 1u << lane;
+	const uint32_t lt = mybit - 1u;
+	const uint32_t le = lt | mybit;
+	const uint32_t n = c.n;
+	uint32_t o = 4;    // output cursor (4 bytes reserved for the size, :291)
+	uint32_t emit = 0; // first input byte not yet emitted (next_emit)
+
+	if (n >= CW_MARGIN) {
+		const uint32_t limit = n - CW_MARGIN;
+		uint32_t q = 1;      // ic layout: where the last match ended; probe layout: position of probe 0
+		bool has_ic = false; // layout of the next pass
+		uint32_t k0 = 0;     // probe layout: step-1 probes already done for this pair
+		for (;;) {
+			if (has_ic && q >= limit) // :386
+				break;
+			CW_STAT(has_ic ? 0 : 1);
+			// ---- lane layout -----------------------------------------------------------------
+			uint32_t p, stride = 1;
+			if (has_ic) {
+				p = q - 1 + lane;
+			} else {
+				const uint32_t K = k0 + lane + 32, s = K >> 5, r = K & 31;
+				p = q + 16u * s * (s - 1) + r * s;
+				stride = s;
+			}
+			const bool dense = has_ic || k0 == 0;
+			bool valid = p + stride <= limit; // :341 (probe), :386 (continuation)
+			if (has_ic && lane == 0)
+				valid = true;
+			// ---- per-lane probe --------------------------------------------------------------
+			uint32_t cur[4] = {0, 0, 0, 0};
+			uint32_t h = 0, tc = 0, cand = 0, mlen = 0;
+			if (valid) {
+				load128u(c.in + p, cur);
+				h = (cur[0] * 0x1e35a7bdu) >> c.shift; // :161-166
+				tc = c.table[h];
+			}
+			wp::syncwarp(); // every lane has read its slot before anyone writes
+			// Speculative insert + read-back: a lane that does not read its own position back shares
+			// its slot with another lane of this pass.
+			uint32_t w1 = p;
+			if (valid) {
+				c.table[h] = (uint16_t)p;
+				cand = tc;
+				mlen = prefix16_fast(c.in, tc, cur);
+			}
+			wp::syncwarp();
+			if (valid)
+				w1 = c.table[h];
+			const uint32_t inval = wp::ballot(!valid);
+			const uint32_t dup1 = wp::ballot(w1 != p);
+			uint32_t same = mybit, lowmask = 0;
+			if (dup1) { // some lanes share a slot: find the groups (second round tells the winners)
+				CW_STAT(6);
+				uint32_t w2 = p;
+				if (valid && w1 != p)
+					c.table[h] = (uint16_t)p;
+				wp::syncwarp();
+				if (valid)
+					w2 = c.table[h];
+				const bool involved = valid && (w1 != p || w2 != p);
+				same = wp::match_any(involved ? h : 0xFFFFFFFFu);
+				if (!involved)
+					same = mybit;
+				lowmask = same & lt;
+				const int src = lowmask ? 31 - wp::clz32(lowmask) : lane;
+				const uint32_t pfwd = wp::shfl(p, src);
+				if (lowmask) { // the closest lower lane with my hash is my candidate (if it is really inserted)
+					cand = pfwd;
+					mlen = prefix16_fast(c.in, cand, cur);
+				}
+			}
+
+			// ---- resolve pairs: uniform walk over ballot masks ---------------------------------
+			const bool hit = valid && mlen >= 4 && !(has_ic && lane == 0);
+			const uint32_t e4 = mlen - 4u; // 0..12 for hit lanes
+			const uint32_t hits = wp::ballot(hit);
+			const uint32_t M0 = wp::ballot(hit && (e4 & 1u)), M1 = wp::ballot(hit && (e4 & 2u)), M2 = wp::ballot(hit && (e4 & 4u)),
+			               M3 = wp::ballot(hit && (e4 & 8u));
+			PassOut r;
+			r.I = r.SK = r.H = r.L = r.LS = r.satbit = r.firstbit = r.lastbit = 0;
+			r.first = true;
+			r.first_generic = false;
+			r.redo = false;
+			r.insbit = has_ic ? 1u : 0u;
+			uint32_t missed = 0; // lanes of an unfinished last pair that were probed and did not hit
+			for (;;) {
+				const uint32_t contbit = r.insbit << 1;
+				const uint32_t above = r.insbit ? 0u - contbit : 0xFFFFFFFFu; // lanes that may hit
+				const uint32_t ab = hits & above;
+				if (!ab) {
+					if (inval) {
+						r.outcome = 2; // :341 / :386 -- the rest of the block is one literal
+						missed = above & ~inval;
+					} else if (r.first) {
+						r.I = 0xFFFFFFFFu; // every lane probed and missed
+						r.outcome = 1;
+					} else {
+						r.outcome = 0; // redo this pair with a window of its own
+						r.redo = true;
+					}
+					break;
+				}
+				CW_STAT(2);
+				const uint32_t fbit = ab & (0u - ab);
+				const uint32_t e = ((M0 & fbit) ? 1u : 0u) | ((M1 & fbit) ? 2u : 0u) | ((M2 & fbit) ? 4u : 0u) | ((M3 & fbit) ? 8u : 0u);
+				r.I |= (fbit << 1) - (r.insbit ? r.insbit : 1u); // lanes ins..f
+				if (r.first && !has_ic) {
+					r.first_generic = true; // the literal started before this window
+				} else {
+					const uint32_t lit = fbit - contbit; // lanes cont..f-1
+					r.L |= lit;
+					if (lit)
+						r.LS |= contbit;
+				}
+				r.H |= fbit;
+				r.lastbit = fbit;
+				if (r.first)
+					r.firstbit = fbit;
+				if (e == 12u) {
+					CW_STAT(4);
+					r.satbit = fbit;
+					r.outcome = 3;
+					break;
+				}
+				const uint32_t nins = fbit << (e + 3u); // lane f + mlen - 1: the next pair's insert lane
+				const bool go = dense && nins != 0u && nins <= (1u << CW_CHAIN_MAX) && ((nins << 1) & ~inval);
+				if (!go) {
+					r.outcome = 0;
+					break;
+				}
+				r.SK |= nins - (fbit << 1); // lanes f+1 .. f+mlen-2
+				r.insbit = nins;
+				r.first = false;
+			}
+			if (dup1) { // was every forwarded candidate really inserted?
+				const bool wrong = (((r.I | missed) >> lane) & 1u) && lowmask && ((r.SK >> (31 - wp::clz32(lowmask))) & 1u);
+				if (wp::ballot(wrong)) {
+					CW_STAT(5);
+					resolve_serial(c, r, has_ic, dense, valid, inval, p, tc, cur, lowmask, cand, mlen, lane);
+				}
+			}
+			if (r.redo)
+				CW_STAT(3);
+#ifdef PIM_WARP_EMU_DEBUG
+			if (lane == 0)
+				fprintf(stderr, "pass q=%u ic=%d k0=%u hits=%08x inval=%08x dup=%08x -> outcome %d redo %d first %d I=%08x H=%08x L=%08x SK=%08x ins=%08x sat=%08x\n", q, (int)has_ic, k0,
+				        hits, inval, dup1, r.outcome, (int)r.redo, (int)r.first, r.I, r.H, r.L, r.SK, r.insbit, r.satbit);
+#endif
+
+			// ---- table: undo the speculative inserts of lanes that were not inserted -----------
+			const bool inI = (r.I >> lane) & 1u;
+			if (r.outcome != 2) {
+				if (valid && !inI)
+					c.table[h] = (uint16_t)tc;
+				if (dup1) { // shared slots: the last inserted lane of the group owns the slot
+					wp::syncwarp();
+					if (inI && !(same & r.I & ~le))
+						c.table[h] = (uint16_t)p;
+				}
+			}
+
+			// ---- where the pass ended ----------------------------------------------------------
+			uint32_t pos_last = 0; // position just past the last complete match / of the long match
+			if (r.outcome == 3)
+				pos_last = wp::reduce_max(mybit == r.satbit ? p : 0u);
+			else if (r.redo || (r.outcome == 2 && !r.first))
+				pos_last = wp::reduce_max(mybit == r.insbit ? p + 1u : 0u);
+			else if (r.outcome == 0)
+				pos_last = wp::reduce_max(mybit == r.lastbit ? p + mlen : 0u);
+
+			// ---- emission --------------------------------------------------------------------
+			if (r.first_generic) {
+				const uint32_t lit_to = wp::reduce_max(mybit == r.firstbit ? p : 0u);
+				o = emit_literal(c, o, emit, lit_to - emit, lane);
+			}
+			const uint32_t Hb = r.H & ~r.satbit;
+			const uint32_t off = p - cand;
+			const bool inHb = (Hb >> lane) & 1u;
+			const bool three = inHb && !(mlen < 12 && off < 2048);
+			const uint32_t H3 = wp::ballot(three);
+			if (r.L | Hb) {
+				const uint32_t pre = wp::popc32(r.L & lt) + wp::popc32(r.LS & le) + 2u * wp::popc32(Hb & lt) + wp::popc32(H3 & lt);
+				uint8_t *dst = c.out + o + pre;
+				if ((r.L >> lane) & 1u) {
+					dst[0] = (uint8_t)cur[0];
+					if ((r.LS >> lane) & 1u) { // literal header: the literal ends at the next hit lane
+						const uint32_t len = (uint32_t)(wp::ffs32(r.H & ~le) - 1 - lane);
+						dst[-1] = (uint8_t)((len - 1) << 2);
+					}
+				} else if (inHb) {
+					if (!three) { // :238-240
+						dst[0] = (uint8_t)(1 + ((mlen - 4) << 2) + ((off >> 8) << 5));
+						dst[1] = (uint8_t)off;
+					} else { // :242-244
+						dst[0] = (uint8_t)(2 + ((mlen - 1) << 2));
+						dst[1] = (uint8_t)off;
+						dst[2] = (uint8_t)(off >> 8);
+					}
+				}
+				o += wp::popc32(r.L) + wp::popc32(r.LS) + 2u * wp::popc32(Hb) + wp::popc32(H3);
+			}
+			int outcome = r.outcome;
+			if (outcome == 3) { // match of >= 16 bytes: extend with the whole warp
+				const uint32_t cf = wp::reduce_max(mybit == r.satbit ? cand : 0u);
+				const uint32_t total = 16u + match_length(c, cf + 16, pos_last + 16, n - pos_last - 16, lane);
+				o = emit_copy(c, o, pos_last - cf, total, lane);
+				q = pos_last + total;
+				emit = q;
+				outcome = 0;
+			} else if (outcome == 0 || (outcome == 2 && !r.first)) {
+				q = pos_last;
+				emit = q;
+			}
+			wp::syncwarp(); // table writes visible to the next pass
+
+			if (outcome == 2)
+				break;
+			if (outcome == 0) {
+				has_ic = true;
+				k0 = 0;
+			} else if (has_ic) { // 30 probes done behind the continuation; probe 0 sat at q+1
+				has_ic = false;
+				q = q + 1;
+				k0 = 30;
+			} else {
+				k0 += 32;
+			}
+		}
+	}
+	if (emit < n) // :405-409
+		o = cw::emit_literal(c, o, emit, n - emit, lane);
+	if (lane < 4) // :411
+		c.out[lane] = (uint8_t)((o - 4) >> (8 * lane));
+	return o;
+}
+
+} // namespace pimsnappy

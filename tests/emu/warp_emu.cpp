@@ -1,0 +1,218 @@
+// Lock-step warp emulator for the per-warp compressor (test infrastructure, CPU only).
+//
+// Compiles pim-compression_b200/csrc/compress_warp.cuh -- the very source the CUDA kernel
+// includes -- with PIM_WARP_EMU, and runs its 32 lanes as 32 cooperative contexts that meet
+// at every warp primitive (ballot / shfl / match_any / syncwarp).  emu_compress() builds the
+// whole file image (header varints + blocks, snappy/README.md:19-33 of the reference) so a
+// test can compare it with the oracle byte for byte without a GPU.
+//
+// Build: g++ -O1 -shared -fPIC -DPIM_WARP_EMU tests/emu/warp_emu.cpp -o tests/emu/_build/libwarp_emu.so
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <ucontext.h>
+#include <vector>
+
+#define PIM_WARP_EMU_STATS
+#include "../../pim-compression_b200/csrc/compress_warp.cuh"
+
+namespace pimsnappy {
+unsigned long cw_stats[8]; // 0 ic passes, 1 probe passes, 2 pairs, 3 redone pairs, 4 long matches, 5 serial re-resolves, 6 passes with shared slots
+}
+extern "C" void emu_set_order(int order);
+extern "C" void emu_stats(unsigned long out[8], int reset)
+{
+	for (int i = 0; i < 8; i++) {
+		out[i] = pimsnappy::cw_stats[i];
+		if (reset)
+			pimsnappy::cw_stats[i] = 0;
+	}
+}
+
+namespace {
+
+constexpr int NL = 32;
+constexpr size_t STACK = 256 * 1024;
+
+ucontext_t g_main, g_ctx[NL];
+int g_cur = 0;
+bool g_done[NL];
+uint32_t g_slot[NL];
+int g_op[NL];          // which primitive each lane is in (divergence check)
+unsigned g_opseq[NL];  // how many primitives each lane has executed
+int g_order = 0; // 0: lanes run 0..31 between primitives (lane 31's store wins a conflict), 1: 31..0, 2: shuffled
+void (*g_body)(void *) = nullptr;
+void *g_arg = nullptr;
+
+void yield() { swapcontext(&g_ctx[g_cur], &g_main); }
+
+void check_converged(int op)
+{
+	for (int l = 0; l < NL; l++) {
+		if (g_done[l] || g_op[l] != op || g_opseq[l] != g_opseq[g_cur]) {
+			fprintf(stderr, "warp_emu: lanes diverged at a warp primitive (lane %d op %d seq %u vs lane %d op %d seq %u%s)\n", g_cur, op,
+			        g_opseq[g_cur], l, g_op[l], g_opseq[l], g_done[l] ? ", finished" : "");
+			abort();
+		}
+	}
+}
+
+// publish v, wait for everyone, return after everyone has read
+template <class F>
+uint32_t exchange(int op, uint32_t v, F &&combine)
+{
+	g_slot[g_cur] = v;
+	g_op[g_cur] = op;
+	g_opseq[g_cur]++;
+	yield(); // every lane has published
+	check_converged(op);
+	const uint32_t r = combine();
+	yield(); // every lane has read
+	return r;
+}
+
+void trampoline()
+{
+	g_body(g_arg);
+	g_done[g_cur] = true;
+	swapcontext(&g_ctx[g_cur], &g_main);
+}
+
+void run_warp(void (*body)(void *), void *arg)
+{
+	static std::vector<char> stacks(NL * STACK);
+	g_body = body;
+	g_arg = arg;
+	for (int l = 0; l < NL; l++) {
+		getcontext(&g_ctx[l]);
+		g_ctx[l].uc_stack.ss_sp = stacks.data() + l * STACK;
+		g_ctx[l].uc_stack.ss_size = STACK;
+		g_ctx[l].uc_link = &g_main;
+		makecontext(&g_ctx[l], trampoline, 0);
+		g_done[l] = false;
+		g_op[l] = -1;
+		g_opseq[l] = 0;
+	}
+	for (;;) {
+		bool any = false;
+		static unsigned rnd = 12345;
+		rnd = rnd * 1664525u + 1013904223u;
+		for (int i = 0; i < NL; i++) {
+			const int l = g_order == 0 ? i : (g_order == 1 ? NL - 1 - i : (int)((i * 13u + (rnd >> 16)) & 31u));
+			if (g_done[l])
+				continue;
+			any = true;
+			g_cur = l;
+			swapcontext(&g_main, &g_ctx[l]);
+		}
+		if (!any)
+			break;
+	}
+}
+
+} // namespace
+
+namespace pimsnappy {
+namespace wp {
+int lane() { return g_cur; }
+uint32_t ballot(bool pred)
+{
+	return exchange(1, pred ? 1u : 0u, [] {
+		uint32_t m = 0;
+		for (int l = 0; l < NL; l++)
+			m |= (g_slot[l] & 1u) << l;
+		return m;
+	});
+}
+uint32_t shfl(uint32_t v, int src_lane)
+{
+	const int s = src_lane & 31;
+	return exchange(2, v, [s] { return g_slot[s]; });
+}
+uint32_t match_any(uint32_t v)
+{
+	return exchange(3, v, [v] {
+		uint32_t m = 0;
+		for (int l = 0; l < NL; l++)
+			m |= (g_slot[l] == v ? 1u : 0u) << l;
+		return m;
+	});
+}
+uint32_t reduce_max(uint32_t v)
+{
+	return exchange(5, v, [] {
+		uint32_t m = 0;
+		for (int l = 0; l < NL; l++)
+			m = g_slot[l] > m ? g_slot[l] : m;
+		return m;
+	});
+}
+void syncwarp()
+{
+	exchange(4, 0, [] { return 0u; });
+}
+} // namespace wp
+} // namespace pimsnappy
+
+namespace {
+
+struct Job {
+	pimsnappy::CBlock blk;
+	uint32_t result;
+};
+
+void body(void *arg)
+{
+	Job *j = static_cast<Job *>(arg);
+	const uint32_t r = pimsnappy::compress_block_warp(j->blk);
+	if (pimsnappy::wp::lane() == 0)
+		j->result = r;
+}
+
+size_t put_varint(uint8_t *p, uint32_t v) // snappy_compress.c:69-98
+{
+	size_t k = 0;
+	while (v >= 128) {
+		p[k++] = (uint8_t)(v | 128);
+		v >>= 7;
+	}
+	p[k++] = (uint8_t)v;
+	return k;
+}
+
+} // namespace
+
+extern "C" void emu_set_order(int order) { g_order = order; }
+
+// Compress in[0..len) into out (capacity >= 32 + len + len/6 + 40 * blocks); returns the file size.
+extern "C" uint64_t emu_compress(const uint8_t *in, uint64_t len, uint32_t block_size, uint8_t *out)
+{
+	using namespace pimsnappy;
+	uint64_t o = put_varint(out, (uint32_t)len);
+	o += put_varint(out + o, block_size);
+	std::vector<uint32_t> tablemem(CW_MAX_TABLE / 2 + 16);
+	std::vector<uint32_t> inmem((block_size + 128) / 4 + 16);
+	std::vector<uint32_t> slotmem((block_size + block_size / 6 + 128) / 4 + 16);
+	for (uint64_t at = 0; at < len; at += block_size) {
+		const uint32_t n = (uint32_t)((len - at < block_size) ? len - at : block_size);
+		// vary the alignment of input and output like the device does (input keeps the global address' low 4 bits)
+		uint8_t *inb = reinterpret_cast<uint8_t *>(inmem.data()) + 32 + (at & 15);
+		memset(inmem.data(), 0xA5, inmem.size() * 4);
+		memcpy(inb, in + at, n);
+		const uint32_t ts = cw_table_entries(n);
+		memset(tablemem.data(), 0, 2 * ts);
+		Job j;
+		j.blk.in = inb;
+		j.blk.table = reinterpret_cast<uint16_t *>(tablemem.data());
+		j.blk.shift = 32 - (31 - __builtin_clz(ts));
+		j.blk.out = reinterpret_cast<uint8_t *>(slotmem.data());
+		j.blk.n = n;
+		j.result = 0;
+		run_warp(body, &j);
+		memcpy(out + o, j.blk.out, j.result);
+		o += j.result;
+	}
+	return o;
+}
