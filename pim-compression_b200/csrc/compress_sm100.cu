@@ -46,13 +46,14 @@ __global__ void __launch_bounds__(32) snappy_compress_kernel(const uint8_t *__re
 	const uint32_t ts = table_entries(n);
 
 	CBlock c;
-	c.in = sm + 2u * ts_max + (uint32_t)(reinterpret_cast<uintptr_t>(gsrc) & 15u);
+	c.inw = reinterpret_cast<const uint32_t *>(sm + 2u * ts_max);
+	c.mis = (uint32_t)(reinterpret_cast<uintptr_t>(gsrc) & 15u);
 	c.table = reinterpret_cast<uint16_t *>(sm);
 	c.shift = 32 - (31 - __clz(ts)); // snappy_compress.c:288
 	c.out = slots + blk * (uint64_t)stride;
 	c.n = n;
 
-	stage_bytes_async(const_cast<uint8_t *>(c.in), gsrc, n, lane, 32);
+	stage_bytes_async(sm + 2u * ts_max + c.mis, gsrc, n, lane, 32);
 	cp_async_commit();
 	for (uint32_t i = lane * 16u; i < 2u * ts; i += 512u)
 		*reinterpret_cast<uint4 *>(sm + i) = make_uint4(0, 0, 0, 0);

@@ -59,27 +59,34 @@ inline uint32_t cw_table_entries(uint32_t n) // snappy_compress.c:139-146
 }
 
 struct CBlock {
-	const uint8_t *in; // input byte 0 (shared memory on the device); 24 readable bytes before/after [0, n)
-	uint16_t *table;   // zeroed, cw_table_entries(n) entries
-	int shift;         // 32 - log2(entries), snappy_compress.c:288
-	uint8_t *out;      // output slot: 4-byte size field + elements
-	uint32_t n;        // input bytes
+	const uint32_t *inw; // 4-byte aligned; input byte i is byte (i + mis) from here (shared memory on the device)
+	uint32_t mis;        // 0..15; 24 readable bytes follow the input
+	uint16_t *table;     // zeroed, cw_table_entries(n) entries
+	int shift;           // 32 - log2(entries), snappy_compress.c:288
+	uint8_t *out;        // output slot: 4-byte size field + elements
+	uint32_t n;          // input bytes
 };
 
 namespace cw {
 
-// four / sixteen bytes at an arbitrary address (aligned word loads + funnel shifts)
-PW_FN uint32_t load32u(const uint8_t *p)
+// Input access goes through word indices only (no pointer <-> integer casts), so that the
+// compiler keeps the shared-memory address space and emits LDS with 32-bit addresses.
+PW_FN uint32_t in_byte(const CBlock &c, uint32_t pos)
 {
-	const uintptr_t a = reinterpret_cast<uintptr_t>(p);
-	const uint32_t *w = reinterpret_cast<const uint32_t *>(a & ~uintptr_t(3));
-	return wp::funnel_r(w[0], w[1], (uint32_t)(a & 3u) * 8u);
+	const uint32_t b = pos + c.mis;
+	return (c.inw[b >> 2] >> ((b & 3u) * 8u)) & 0xFFu;
 }
-PW_FN void load128u(const uint8_t *p, uint32_t v[4])
+PW_FN uint32_t in_load32(const CBlock &c, uint32_t pos)
 {
-	const uintptr_t a = reinterpret_cast<uintptr_t>(p);
-	const uint32_t *w = reinterpret_cast<const uint32_t *>(a & ~uintptr_t(3));
-	const uint32_t sh = (uint32_t)(a & 3u) * 8u;
+	const uint32_t b = pos + c.mis;
+	const uint32_t *w = c.inw + (b >> 2);
+	return wp::funnel_r(w[0], w[1], (b & 3u) * 8u);
+}
+PW_FN void in_load128(const CBlock &c, uint32_t pos, uint32_t v[4])
+{
+	const uint32_t b = pos + c.mis;
+	const uint32_t *w = c.inw + (b >> 2);
+	const uint32_t sh = (b & 3u) * 8u;
 	const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
 	v[0] = wp::funnel_r(w0, w1, sh);
 	v[1] = wp::funnel_r(w1, w2, sh);
@@ -87,19 +94,17 @@ PW_FN void load128u(const uint8_t *p, uint32_t v[4])
 	v[3] = wp::funnel_r(w3, w4, sh);
 }
 
-// number of equal leading bytes (0..16) of in[cand..] and the sixteen bytes `cur`
-PW_FN uint32_t common_prefix16(const uint8_t *in, uint32_t cand, const uint32_t cur[4])
+// number of equal leading bytes (0..16) of in[cand..] and the sixteen bytes `cur`; no FLO/BREV
+// (those cost ~40 cycles on the pass's critical path)
+PW_FN uint32_t common_prefix16(const CBlock &c, uint32_t cand, const uint32_t cur[4])
 {
 	uint32_t cwd[4];
-	load128u(in + cand, cwd);
-	uint32_t m = 16;
-#pragma unroll
-	for (int w = 3; w >= 0; w--) {
-		const uint32_t d = cur[w] ^ cwd[w];
-		if (d)
-			m = 4u * w + ((uint32_t)(wp::ffs32(d) - 1) >> 3);
-	}
-	return m;
+	in_load128(c, cand, cwd);
+	const uint32_t d0 = cur[0] ^ cwd[0], d1 = cur[1] ^ cwd[1], d2 = cur[2] ^ cwd[2], d3 = cur[3] ^ cwd[3];
+	const uint32_t d = d0 ? d0 : (d1 ? d1 : (d2 ? d2 : d3));
+	const uint32_t base = d0 ? 0u : (d1 ? 4u : (d2 ? 8u : 12u));
+	const uint32_t inword = ((d & 0xFFu) == 0u) + ((d & 0xFFFFu) == 0u) + ((d & 0xFFFFFFu) == 0u);
+	return d ? base + inword : 16u;
 }
 
 // lanes a..b inclusive (empty if b < a); 0 <= a, b <= 31
@@ -126,19 +131,18 @@ PW_FN uint32_t emit_literal(const CBlock &c, uint32_t o, uint32_t from, uint32_t
 			c.out[o + 1 + lane] = (uint8_t)(n1 >> (8 * lane));
 	}
 	uint8_t *dst = c.out + o + hdr;
-	const uint8_t *src = c.in + from;
 	uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u;
 	if (head > len)
 		head = len;
 	if ((uint32_t)lane < head)
-		dst[lane] = src[lane];
+		dst[lane] = (uint8_t)in_byte(c, from + lane);
 	const uint32_t words = (len - head) >> 2;
 	uint32_t *d32 = reinterpret_cast<uint32_t *>(dst + head);
 	for (uint32_t i = lane; i < words; i += 32)
-		d32[i] = load32u(src + head + 4u * i);
+		d32[i] = in_load32(c, from + head + 4u * i);
 	const uint32_t done = head + 4u * words;
 	if (done + lane < len)
-		dst[done + lane] = src[done + lane];
+		dst[done + lane] = (uint8_t)in_byte(c, from + done + lane);
 	return o + hdr + len;
 }
 
@@ -193,8 +197,8 @@ PW_FN uint32_t match_length(const CBlock &c, uint32_t a, uint32_t b, uint32_t ma
 		uint32_t cnt = 0; // equal bytes at the front of this lane's 16
 		if (j < maxn) {
 			uint32_t x[4];
-			load128u(c.in + b + j, x);
-			cnt = wp::umin(common_prefix16(c.in, a + j, x), maxn - j);
+			in_load128(c, b + j, x);
+			cnt = wp::umin(common_prefix16(c, a + j, x), maxn - j);
 		}
 		const uint32_t stop = wp::ballot(cnt < 16);
 		if (stop) {
@@ -204,102 +208,116 @@ PW_FN uint32_t match_length(const CBlock &c, uint32_t a, uint32_t b, uint32_t ma
 	}
 }
 
-} // namespace cw
+constexpr uint32_t CW_SAT = 0xFFFFFFFFu; // "next insert lane" of a hit lane whose match is >= 16 bytes
 
-namespace cw {
-
-// number of equal leading bytes (0..16) without FLO/BREV (those cost ~40 cycles on the chain)
-PW_FN uint32_t prefix16_fast(const uint8_t *in, uint32_t cand, const uint32_t cur[4])
-{
-	uint32_t cwd[4];
-	load128u(in + cand, cwd);
-	const uint32_t d0 = cur[0] ^ cwd[0], d1 = cur[1] ^ cwd[1], d2 = cur[2] ^ cwd[2], d3 = cur[3] ^ cwd[3];
-	const uint32_t d = d0 ? d0 : (d1 ? d1 : (d2 ? d2 : d3));
-	const uint32_t base = d0 ? 0u : (d1 ? 4u : (d2 ? 8u : (d3 ? 12u : 16u)));
-	const uint32_t inword = ((d & 0xFFu) == 0u) + ((d & 0xFFFFu) == 0u) + ((d & 0xFFFFFFu) == 0u); // d == 0 only when base == 16
-	return d ? base + inword : 16u;
-}
-
-// What a pass decided (uniform across the warp).
-struct PassOut {
-	uint32_t I;        // lanes whose positions are inserted into the table
-	uint32_t SK;       // lanes inside a match (never probed, never inserted)
+// What the pair walk of one pass decided (uniform across the warp).
+struct Walk {
+	uint32_t V;        // insert lanes: lane 0 in the ic layout, then lane f+mlen-1 of every match the walk continued after
 	uint32_t H;        // hit lanes
-	uint32_t L, LS;    // in-window literal bytes / first byte of each such literal
-	uint32_t satbit;   // hit lane whose match is >= 16 bytes (its copy is emitted by the extension path), else 0
-	uint32_t firstbit; // first hit lane of the pass
-	uint32_t lastbit;  // last hit lane
-	uint32_t insbit;   // insert lane of the pair the pass stopped in (0: none)
-	bool first;        // the pass stopped in its first pair
-	bool first_generic;// the first pair's literal started before the window
+	uint32_t firstbit; // first hit lane (0: none)
+	uint32_t lastbit;  // last hit lane (0: none)
+	uint32_t satbit;   // hit lane whose match is >= 16 bytes (always the last one), else 0
+	uint32_t insbit;   // insert lane of the pair the walk stopped in (0: none)
+	bool first;        // the walk stopped in the pass's first pair
+	bool redo;         // outcome 0 without a hit: the pair the walk stopped in gets a pass of its own
 	int outcome;       // 0: next pass in ic layout   1: keep probing   2: remainder   3: long match at satbit
-	bool redo;         // outcome 0 without a hit: redo the pair the pass stopped in
 };
 
-// Serial, always-exact resolution of the pairs of one pass: used when a lane's forwarded candidate
-// (a lower lane of the same pass with the same hash) turns out to lie inside a match.  cand / mlen
-// of a lane are re-evaluated whenever the set of skipped lanes changes its closest inserted lane.
-PW_FN void resolve_serial(const CBlock &c, PassOut &r, bool has_ic, bool dense, bool valid, uint32_t inval, uint32_t p, uint32_t tc,
-                          const uint32_t cur[4], uint32_t lowmask, uint32_t &cand, uint32_t &mlen, int lane)
+// Fast walk: every lane's candidate is fixed (table entry, or the closest lower lane with the same
+// hash); one warp reduction per pair fetches the hit lane's "next insert lane".
+PW_FN void walk_fast(Walk &w, bool has_ic, bool dense, uint32_t hits, uint32_t inval, uint32_t mynins, uint32_t mybit)
 {
-	r.I = r.SK = r.H = r.L = r.LS = r.satbit = r.firstbit = r.lastbit = 0;
-	r.first = true;
-	r.first_generic = false;
-	r.redo = false;
+	w.V = has_ic ? 1u : 0u;
+	w.H = w.firstbit = w.lastbit = w.satbit = 0;
+	w.insbit = w.V;
+	w.first = true;
+	w.redo = false;
+	uint32_t above = has_ic ? ~1u : ~0u; // lanes that may hit in the current pair
+	for (;;) {
+		const uint32_t ab = hits & above;
+		if (!ab) {
+			// inval: :341 / :386, the rest of the block is one literal.  Otherwise the window is
+			// exhausted: a first pair keeps probing, a later pair is redone with a window of its own.
+			w.outcome = inval ? 2 : (w.first ? 1 : 0);
+			w.redo = !inval && !w.first;
+			return;
+		}
+		CW_STAT(2);
+		const uint32_t fbit = ab & (0u - ab);
+		const uint32_t nv = wp::reduce_max(mybit == fbit ? mynins : 0u);
+		w.H |= fbit;
+		w.lastbit = fbit;
+		if (w.first)
+			w.firstbit = fbit;
+		if (nv == CW_SAT) {
+			CW_STAT(4);
+			w.satbit = fbit;
+			w.outcome = 3;
+			return;
+		}
+		// continue in this pass if the next pair's insert lane and continuation lane are usable
+		const bool go = dense && nv != 0u && nv <= (1u << CW_CHAIN_MAX) && ((nv << 1) & ~inval);
+		if (!go) {
+			w.outcome = 0;
+			return;
+		}
+		w.V |= nv;
+		w.insbit = nv;
+		above = 0u - (nv << 1);
+		w.first = false;
+	}
+}
+
+// Serial, always-exact walk: used when a lane's forwarded candidate (a lower lane of the same pass
+// with the same hash) turned out to lie inside a match.  cand / mlen of a lane are re-evaluated
+// whenever the set of skipped lanes changes its closest inserted lane.  Dense passes only.
+PW_FN void walk_serial(const CBlock &c, Walk &w, bool has_ic, bool valid, uint32_t inval, uint32_t p, uint32_t tc, const uint32_t cur[4],
+                       uint32_t lowmask, uint32_t &cand, uint32_t &mlen, int lane)
+{
+	w.V = has_ic ? 1u : 0u;
+	w.H = w.firstbit = w.lastbit = w.satbit = 0;
+	w.first = true;
+	w.redo = false;
+	uint32_t SK = 0; // lanes inside a match (never inserted)
 	int ins = has_ic ? 0 : -1;
 	int loaded = -2; // force an evaluation in the first round
 	for (;;) {
 		const int cont = ins + 1;
-		const uint32_t eff = lowmask & ~r.SK;
+		const uint32_t eff = lowmask & ~SK;
 		const int want = eff ? 31 - wp::clz32(eff) : -1;
 		if (want != loaded && valid) {
 			loaded = want;
-			cand = want < 0 ? tc : p - lane + want; // forwarding only happens in dense passes
-			mlen = common_prefix16(c.in, cand, cur);
+			cand = want < 0 ? tc : p - lane + want;
+			mlen = common_prefix16(c, cand, cur);
 		}
 		const uint32_t hits = wp::ballot(valid && lane >= cont && mlen >= 4);
-		r.insbit = ins < 0 ? 0u : 1u << ins;
+		w.insbit = ins < 0 ? 0u : 1u << ins;
 		if (!hits) {
-			if (inval) {
-				r.outcome = 2;
-			} else if (r.first) {
-				r.I = 0xFFFFFFFFu;
-				r.outcome = 1;
-			} else {
-				r.outcome = 0;
-				r.redo = true;
-			}
+			w.outcome = inval ? 2 : (w.first ? 1 : 0);
+			w.redo = !inval && !w.first;
 			return;
 		}
 		const int f = wp::ffs32(hits) - 1;
-		r.I |= lanes(ins < 0 ? 0 : ins, f);
 		const uint32_t mf = wp::shfl(mlen, f);
-		if (r.first && !has_ic) {
-			r.first_generic = true;
-		} else {
-			const uint32_t lit = lanes(cont, f - 1);
-			r.L |= lit;
-			if (lit)
-				r.LS |= 1u << cont;
-		}
-		r.H |= 1u << f;
-		r.lastbit = 1u << f;
-		if (r.first)
-			r.firstbit = 1u << f;
+		w.H |= 1u << f;
+		w.lastbit = 1u << f;
+		if (w.first)
+			w.firstbit = 1u << f;
 		if (mf == 16) {
-			r.satbit = 1u << f;
-			r.outcome = 3;
+			w.satbit = 1u << f;
+			w.outcome = 3;
 			return;
 		}
 		const int ins2 = f + (int)mf - 1;
-		const bool go = dense && ins2 <= CW_CHAIN_MAX && !((inval >> (ins2 + 1)) & 1u);
+		const bool go = ins2 <= CW_CHAIN_MAX && !((inval >> (ins2 + 1)) & 1u);
 		if (!go) {
-			r.outcome = 0;
+			w.outcome = 0;
 			return;
 		}
-		r.SK |= lanes(f + 1, ins2 - 1);
+		SK |= lanes(f + 1, ins2 - 1);
+		w.V |= 1u << ins2;
 		ins = ins2;
-		r.first = false;
+		w.first = false;
 	}
 }
 
@@ -343,7 +361,7 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 			uint32_t cur[4] = {0, 0, 0, 0};
 			uint32_t h = 0, tc = 0, cand = 0, mlen = 0;
 			if (valid) {
-				load128u(c.in + p, cur);
+				in_load128(c, p, cur);
 				h = (cur[0] * 0x1e35a7bdu) >> c.shift; // :161-166
 				tc = c.table[h];
 			}
@@ -354,7 +372,7 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 			if (valid) {
 				c.table[h] = (uint16_t)p;
 				cand = tc;
-				mlen = prefix16_fast(c.in, tc, cur);
+				mlen = common_prefix16(c, tc, cur);
 			}
 			wp::syncwarp();
 			if (valid)
@@ -362,7 +380,7 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 			const uint32_t inval = wp::ballot(!valid);
 			const uint32_t dup1 = wp::ballot(w1 != p);
 			uint32_t same = mybit, lowmask = 0;
-			if (dup1) { // some lanes share a slot: find the groups (second round tells the winners)
+			if (dup1) { // some lanes share a slot: find the groups (a second round tells the winners)
 				CW_STAT(6);
 				uint32_t w2 = p;
 				if (valid && w1 != p)
@@ -379,148 +397,109 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 				const uint32_t pfwd = wp::shfl(p, src);
 				if (lowmask) { // the closest lower lane with my hash is my candidate (if it is really inserted)
 					cand = pfwd;
-					mlen = prefix16_fast(c.in, cand, cur);
+					mlen = common_prefix16(c, cand, cur);
 				}
 			}
 
-			// ---- resolve pairs: uniform walk over ballot masks ---------------------------------
-			const bool hit = valid && mlen >= 4 && !(has_ic && lane == 0);
-			const uint32_t e4 = mlen - 4u; // 0..12 for hit lanes
-			const uint32_t hits = wp::ballot(hit);
-			const uint32_t M0 = wp::ballot(hit && (e4 & 1u)), M1 = wp::ballot(hit && (e4 & 2u)), M2 = wp::ballot(hit && (e4 & 4u)),
-			               M3 = wp::ballot(hit && (e4 & 8u));
-			PassOut r;
-			r.I = r.SK = r.H = r.L = r.LS = r.satbit = r.firstbit = r.lastbit = 0;
-			r.first = true;
-			r.first_generic = false;
-			r.redo = false;
-			r.insbit = has_ic ? 1u : 0u;
-			uint32_t missed = 0; // lanes of an unfinished last pair that were probed and did not hit
-			for (;;) {
-				const uint32_t contbit = r.insbit << 1;
-				const uint32_t above = r.insbit ? 0u - contbit : 0xFFFFFFFFu; // lanes that may hit
-				const uint32_t ab = hits & above;
-				if (!ab) {
-					if (inval) {
-						r.outcome = 2; // :341 / :386 -- the rest of the block is one literal
-						missed = above & ~inval;
-					} else if (r.first) {
-						r.I = 0xFFFFFFFFu; // every lane probed and missed
-						r.outcome = 1;
-					} else {
-						r.outcome = 0; // redo this pair with a window of its own
-						r.redo = true;
-					}
-					break;
-				}
-				CW_STAT(2);
-				const uint32_t fbit = ab & (0u - ab);
-				const uint32_t e = ((M0 & fbit) ? 1u : 0u) | ((M1 & fbit) ? 2u : 0u) | ((M2 & fbit) ? 4u : 0u) | ((M3 & fbit) ? 8u : 0u);
-				r.I |= (fbit << 1) - (r.insbit ? r.insbit : 1u); // lanes ins..f
-				if (r.first && !has_ic) {
-					r.first_generic = true; // the literal started before this window
+			// ---- resolve the pairs of this pass ------------------------------------------------
+			Walk w;
+			bool inI;       // my position is inserted into the table
+			uint32_t Imask;
+			for (bool serial = false;; serial = true) {
+				if (!serial) {
+					const bool hit = valid && mlen >= 4 && !(has_ic && lane == 0);
+					const uint32_t mynins = hit ? (mlen == 16 ? CW_SAT : mybit << (mlen - 1)) : 0u;
+					walk_fast(w, has_ic, dense, wp::ballot(hit), inval, mynins, mybit);
 				} else {
-					const uint32_t lit = fbit - contbit; // lanes cont..f-1
-					r.L |= lit;
-					if (lit)
-						r.LS |= contbit;
-				}
-				r.H |= fbit;
-				r.lastbit = fbit;
-				if (r.first)
-					r.firstbit = fbit;
-				if (e == 12u) {
-					CW_STAT(4);
-					r.satbit = fbit;
-					r.outcome = 3;
-					break;
-				}
-				const uint32_t nins = fbit << (e + 3u); // lane f + mlen - 1: the next pair's insert lane
-				const bool go = dense && nins != 0u && nins <= (1u << CW_CHAIN_MAX) && ((nins << 1) & ~inval);
-				if (!go) {
-					r.outcome = 0;
-					break;
-				}
-				r.SK |= nins - (fbit << 1); // lanes f+1 .. f+mlen-2
-				r.insbit = nins;
-				r.first = false;
-			}
-			if (dup1) { // was every forwarded candidate really inserted?
-				const bool wrong = (((r.I | missed) >> lane) & 1u) && lowmask && ((r.SK >> (31 - wp::clz32(lowmask))) & 1u);
-				if (wp::ballot(wrong)) {
 					CW_STAT(5);
-					resolve_serial(c, r, has_ic, dense, valid, inval, p, tc, cur, lowmask, cand, mlen, lane);
+					walk_serial(c, w, has_ic, valid, inval, p, tc, cur, lowmask, cand, mlen, lane);
 				}
+				// a lane was probed iff the closest marker at or below it is an insert lane (not a hit lane)
+				const uint32_t Vle = w.V & le, Hlt = w.H & lt;
+				const bool probed = Vle > Hlt || Hlt == 0u;
+				inI = w.outcome == 1 || (probed && mybit <= w.lastbit);
+				Imask = wp::ballot(inI);
+				if (!dup1 || serial)
+					break;
+				// was every forwarded candidate really inserted (or probed, in an unfinished last pair)?
+				const bool evaluated = inI || (w.outcome == 2 && valid && mybit > w.insbit);
+				const uint32_t E = wp::ballot(evaluated);
+				const bool wrong = evaluated && lowmask && !((E >> (31 - wp::clz32(lowmask))) & 1u);
+				if (!wp::ballot(wrong))
+					break;
 			}
-			if (r.redo)
+			if (w.redo)
 				CW_STAT(3);
-#ifdef PIM_WARP_EMU_DEBUG
-			if (lane == 0)
-				fprintf(stderr, "pass q=%u ic=%d k0=%u hits=%08x inval=%08x dup=%08x -> outcome %d redo %d first %d I=%08x H=%08x L=%08x SK=%08x ins=%08x sat=%08x\n", q, (int)has_ic, k0,
-				        hits, inval, dup1, r.outcome, (int)r.redo, (int)r.first, r.I, r.H, r.L, r.SK, r.insbit, r.satbit);
-#endif
 
 			// ---- table: undo the speculative inserts of lanes that were not inserted -----------
-			const bool inI = (r.I >> lane) & 1u;
-			if (r.outcome != 2) {
+			if (w.outcome != 2) {
 				if (valid && !inI)
 					c.table[h] = (uint16_t)tc;
 				if (dup1) { // shared slots: the last inserted lane of the group owns the slot
 					wp::syncwarp();
-					if (inI && !(same & r.I & ~le))
+					if (inI && !(same & Imask & ~le))
 						c.table[h] = (uint16_t)p;
 				}
 			}
 
 			// ---- where the pass ended ----------------------------------------------------------
-			uint32_t pos_last = 0; // position just past the last complete match / of the long match
-			if (r.outcome == 3)
-				pos_last = wp::reduce_max(mybit == r.satbit ? p : 0u);
-			else if (r.redo || (r.outcome == 2 && !r.first))
-				pos_last = wp::reduce_max(mybit == r.insbit ? p + 1u : 0u);
-			else if (r.outcome == 0)
-				pos_last = wp::reduce_max(mybit == r.lastbit ? p + mlen : 0u);
+			const bool by_ins = w.redo || (w.outcome == 2 && !w.first); // just past the last complete match
+			const bool have_pos = by_ins || w.outcome == 0 || w.outcome == 3;
+			uint32_t pos_last = 0;
+			if (have_pos) {
+				const uint32_t sel = by_ins ? w.insbit : w.lastbit;
+				const uint32_t add = by_ins ? 1u : (w.outcome == 3 ? 0u : mlen);
+				pos_last = wp::reduce_max(mybit == sel ? p + add : 0u);
+			}
 
 			// ---- emission --------------------------------------------------------------------
-			if (r.first_generic) {
-				const uint32_t lit_to = wp::reduce_max(mybit == r.firstbit ? p : 0u);
+			if (!has_ic && w.firstbit) { // the first pair's literal started before this window
+				const uint32_t lit_to = wp::reduce_max(mybit == w.firstbit ? p : 0u);
 				o = emit_literal(c, o, emit, lit_to - emit, lane);
 			}
-			const uint32_t Hb = r.H & ~r.satbit;
+			const uint32_t before_last = w.lastbit ? w.lastbit - 1u : 0u;
+			const uint32_t first_region = has_ic ? 0u : w.firstbit - 1u; // (firstbit == 0: nothing is emitted anyway)
+			const uint32_t L = Imask & ~w.H & ~w.V & ~first_region & before_last; // in-window literal bytes
+			const uint32_t LS = L & (w.V << 1);                                   // first byte of each such literal
+			const uint32_t Hb = w.H & ~w.satbit;                                  // hit lanes whose tag is written here
 			const uint32_t off = p - cand;
 			const bool inHb = (Hb >> lane) & 1u;
 			const bool three = inHb && !(mlen < 12 && off < 2048);
 			const uint32_t H3 = wp::ballot(three);
-			if (r.L | Hb) {
-				const uint32_t pre = wp::popc32(r.L & lt) + wp::popc32(r.LS & le) + 2u * wp::popc32(Hb & lt) + wp::popc32(H3 & lt);
+			if (L | Hb) {
+				const uint32_t pre = wp::popc32((L | Hb) & lt) + wp::popc32((LS & le) | (Hb & lt)) + wp::popc32(H3 & lt);
 				uint8_t *dst = c.out + o + pre;
-				if ((r.L >> lane) & 1u) {
+				if ((L >> lane) & 1u) {
 					dst[0] = (uint8_t)cur[0];
-					if ((r.LS >> lane) & 1u) { // literal header: the literal ends at the next hit lane
-						const uint32_t len = (uint32_t)(wp::ffs32(r.H & ~le) - 1 - lane);
-						dst[-1] = (uint8_t)((len - 1) << 2);
+				} else if ((w.H >> lane) & 1u) {
+					const uint32_t vlow = w.V & lt;
+					if (vlow) { // literal header: the literal runs from behind the pair's insert lane to me
+						const uint32_t litlen = (uint32_t)lane - 1u - (uint32_t)(31 - wp::clz32(vlow));
+						if (litlen)
+							dst[-(int)litlen - 1] = (uint8_t)((litlen - 1) << 2);
 					}
-				} else if (inHb) {
-					if (!three) { // :238-240
-						dst[0] = (uint8_t)(1 + ((mlen - 4) << 2) + ((off >> 8) << 5));
-						dst[1] = (uint8_t)off;
-					} else { // :242-244
-						dst[0] = (uint8_t)(2 + ((mlen - 1) << 2));
-						dst[1] = (uint8_t)off;
-						dst[2] = (uint8_t)(off >> 8);
+					if (inHb) {
+						if (!three) { // :238-240
+							dst[0] = (uint8_t)(1 + ((mlen - 4) << 2) + ((off >> 8) << 5));
+							dst[1] = (uint8_t)off;
+						} else { // :242-244
+							dst[0] = (uint8_t)(2 + ((mlen - 1) << 2));
+							dst[1] = (uint8_t)off;
+							dst[2] = (uint8_t)(off >> 8);
+						}
 					}
 				}
-				o += wp::popc32(r.L) + wp::popc32(r.LS) + 2u * wp::popc32(Hb) + wp::popc32(H3);
+				o += wp::popc32(L | Hb) + wp::popc32(LS | Hb) + wp::popc32(H3);
 			}
-			int outcome = r.outcome;
+			int outcome = w.outcome;
 			if (outcome == 3) { // match of >= 16 bytes: extend with the whole warp
-				const uint32_t cf = wp::reduce_max(mybit == r.satbit ? cand : 0u);
+				const uint32_t cf = wp::reduce_max(mybit == w.satbit ? cand : 0u);
 				const uint32_t total = 16u + match_length(c, cf + 16, pos_last + 16, n - pos_last - 16, lane);
 				o = emit_copy(c, o, pos_last - cf, total, lane);
 				q = pos_last + total;
 				emit = q;
 				outcome = 0;
-			} else if (outcome == 0 || (outcome == 2 && !r.first)) {
+			} else if (have_pos) {
 				q = pos_last;
 				emit = q;
 			}

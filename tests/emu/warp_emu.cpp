@@ -198,13 +198,14 @@ extern "C" uint64_t emu_compress(const uint8_t *in, uint64_t len, uint32_t block
 	for (uint64_t at = 0; at < len; at += block_size) {
 		const uint32_t n = (uint32_t)((len - at < block_size) ? len - at : block_size);
 		// vary the alignment of input and output like the device does (input keeps the global address' low 4 bits)
-		uint8_t *inb = reinterpret_cast<uint8_t *>(inmem.data()) + 32 + (at & 15);
+		uint8_t *inb = reinterpret_cast<uint8_t *>(inmem.data() + 8) + (at & 15);
 		memset(inmem.data(), 0xA5, inmem.size() * 4);
 		memcpy(inb, in + at, n);
 		const uint32_t ts = cw_table_entries(n);
 		memset(tablemem.data(), 0, 2 * ts);
 		Job j;
-		j.blk.in = inb;
+		j.blk.inw = inmem.data() + 8;
+		j.blk.mis = (uint32_t)(at & 15);
 		j.blk.table = reinterpret_cast<uint16_t *>(tablemem.data());
 		j.blk.shift = 32 - (31 - __builtin_clz(ts));
 		j.blk.out = reinterpret_cast<uint8_t *>(slotmem.data());
