@@ -107,6 +107,13 @@ void pim_snappy_host_free(void *p);
 int pim_snappy_set_devices(const int *device_ids, int n);
 int pim_snappy_device_count(void);
 
+/* The host entry points stream shards larger than two chunks: chunk i+1 is
+ * copied to the device while chunk i is coded and chunk i-1 is copied back
+ * (what the reference's separate copy_in / run / copy_out phases,
+ * snappy_compress.c:560-670, become when they overlap).  Default 128 MiB, or
+ * $PIM_SNAPPY_CHUNK_MIB; 0 processes every shard in one piece. */
+void pim_snappy_set_chunk_bytes(uint64_t bytes);
+
 /* Largest block size of the format's valid domain. */
 #define PIM_SNAPPY_MAX_BLOCK_SIZE 65536u
 

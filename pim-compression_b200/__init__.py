@@ -30,6 +30,7 @@ from .api import (  # noqa: F401
     synth_host,
     synth_device,
     set_devices,
+    set_chunk_bytes,
     device_count,
     launch_count,
     profile,

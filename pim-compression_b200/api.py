@@ -71,6 +71,7 @@ def lib() -> C.CDLL:
         "pim_snappy_host_free": (None, [C.c_void_p]),
         "pim_snappy_set_devices": (C.c_int, [P(C.c_int), C.c_int]),
         "pim_snappy_device_count": (C.c_int, []),
+        "pim_snappy_set_chunk_bytes": (None, [C.c_uint64]),
         "pim_snappy_num_blocks": (C.c_uint64, [C.c_uint64, C.c_uint32]),
         "pim_snappy_compress_bound": (C.c_uint64, [C.c_uint64, C.c_uint32]),
         "pim_snappy_compress_scratch_bytes": (C.c_uint64, [C.c_uint64, C.c_uint32]),
@@ -94,7 +95,7 @@ def lib() -> C.CDLL:
 EXPORTED_SYMBOLS = [
     "setup_compression", "setup_decompression", "snappy_compress_dpu", "snappy_decompress_dpu",
     "snappy_compress_gpu", "snappy_decompress_gpu", "get_runtime", "pim_snappy_host_alloc", "pim_snappy_host_free",
-    "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
+    "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_set_chunk_bytes", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
     "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_decompress_device",
     "pim_snappy_launch_count", "pim_snappy_profile", "pim_snappy_profile_read", "pim_snappy_synth_host", "pim_snappy_synth_device", "pim_snappy_version",
 ]
@@ -103,6 +104,11 @@ EXPORTED_SYMBOLS = [
 def set_devices(ids) -> int:
     arr = (C.c_int * len(ids))(*ids)
     return int(lib().pim_snappy_set_devices(arr, len(ids)))
+
+
+def set_chunk_bytes(n: int) -> None:
+    """Chunk size of the streamed host path (0: whole shard in one piece)."""
+    lib().pim_snappy_set_chunk_bytes(n)
 
 
 def device_count() -> int:

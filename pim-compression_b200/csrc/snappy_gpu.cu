@@ -100,6 +100,12 @@ struct DeviceCtx {
 	uint64_t *d_off = nullptr; size_t cap_off = 0;  // block offsets (entries)
 	uint32_t *d_status = nullptr;
 	uint64_t *h_small = nullptr;                    // pinned: [0] total, [1] status
+	// chunked pipeline (H2D | kernels | D2H on three streams, two buffers each)
+	cudaStream_t s_in = nullptr, s_out = nullptr;
+	cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+	cudaEvent_t ev_span[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // first/last of each stream
+	uint64_t *h_pin = nullptr; size_t cap_pin = 0;  // pinned: per-chunk totals / block offsets (entries)
+	uint32_t *d_statv = nullptr; size_t cap_statv = 0;
 };
 
 std::mutex g_dev_mu;
@@ -122,8 +128,15 @@ int init_devices_locked(const int *ids, int n)
 		cudaSetDevice(d.dev);
 		if (d.stream) cudaStreamDestroy(d.stream);
 		for (auto &e : d.ev) if (e) cudaEventDestroy(e);
-		cudaFree(d.d_a); cudaFree(d.d_b); cudaFree(d.d_scratch); cudaFree(d.d_off); cudaFree(d.d_status);
+		cudaFree(d.d_a); cudaFree(d.d_b); cudaFree(d.d_scratch); cudaFree(d.d_off); cudaFree(d.d_status); cudaFree(d.d_statv);
 		if (d.h_small) cudaFreeHost(d.h_small);
+		if (d.h_pin) cudaFreeHost(d.h_pin);
+		if (d.s_in) cudaStreamDestroy(d.s_in);
+		if (d.s_out) cudaStreamDestroy(d.s_out);
+		for (auto &e : d.ev_in) if (e) cudaEventDestroy(e);
+		for (auto &e : d.ev_k) if (e) cudaEventDestroy(e);
+		for (auto &e : d.ev_out) if (e) cudaEventDestroy(e);
+		for (auto &e : d.ev_span) if (e) cudaEventDestroy(e);
 	}
 	g_devs.clear();
 	std::vector<int> want;
@@ -151,6 +164,12 @@ int init_devices_locked(const int *ids, int n)
 		if (cudaSetDevice(id) != cudaSuccess) continue;
 		if (cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess) continue;
 		for (auto &e : d.ev) cudaEventCreate(&e);
+		if (cudaStreamCreateWithFlags(&d.s_in, cudaStreamNonBlocking) != cudaSuccess) continue;
+		if (cudaStreamCreateWithFlags(&d.s_out, cudaStreamNonBlocking) != cudaSuccess) continue;
+		for (auto &e : d.ev_in) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+		for (auto &e : d.ev_k) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+		for (auto &e : d.ev_out) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+		for (auto &e : d.ev_span) cudaEventCreate(&e);
 		cudaMalloc(&d.d_status, 256);
 		cudaHostAlloc(&d.h_small, 256, cudaHostAllocDefault);
 		g_devs.push_back(d);
@@ -183,6 +202,38 @@ bool grow(T *&p, size_t &cap, size_t need)
 	}
 	cap = need;
 	return true;
+}
+
+bool grow_pinned(uint64_t *&p, size_t &cap, size_t need)
+{
+	if (need <= cap)
+		return true;
+	if (p)
+		cudaFreeHost(p);
+	p = nullptr;
+	cap = 0;
+	need = (need + (need >> 2) + 511) & ~size_t(511);
+	if (cudaHostAlloc(&p, need * sizeof(uint64_t), cudaHostAllocDefault) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	cap = need;
+	return true;
+}
+
+// Shards larger than two chunks are streamed: chunk i+1 is copied in while chunk i is coded and
+// chunk i-1 is copied out.  $PIM_SNAPPY_CHUNK_MIB overrides the chunk size (0 disables streaming).
+std::atomic<uint64_t> g_chunk_bytes{~uint64_t(0)}; // ~0: not set yet
+uint64_t chunk_bytes()
+{
+	uint64_t v = g_chunk_bytes.load(std::memory_order_relaxed);
+	if (v == ~uint64_t(0)) {
+		const char *e = getenv("PIM_SNAPPY_CHUNK_MIB");
+		const long mib = e ? atol(e) : 128;
+		v = mib <= 0 ? uint64_t(0) : uint64_t(mib) << 20;
+		g_chunk_bytes.store(v, std::memory_order_relaxed);
+	}
+	return v;
 }
 
 size_t put_varint32(uint8_t *p, uint32_t v) // snappy_compress.c:69-98
@@ -235,6 +286,156 @@ void for_each_shard(int ng, F &&fn)
 		th.emplace_back([&, g] { fn(g); });
 	for (auto &t : th)
 		t.join();
+}
+
+inline uint64_t align256(uint64_t v) { return (v + 255) & ~uint64_t(255); }
+
+// Compress one shard (a whole number of blocks) as a stream of chunks: H2D of chunk i+1, the
+// kernels of chunk i and the D2H of chunk i-1 run concurrently on three streams.  The compressed
+// chunks land back to back at host_out.  Returns the shard's compressed bytes in *total.
+int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_bytes, uint32_t block_size, uint8_t *host_out,
+                            uint64_t *total, ShardTimes &tm)
+{
+	const uint64_t cblocks = std::max<uint64_t>(1, chunk_bytes() / block_size);
+	const uint64_t cin = cblocks * block_size; // input bytes per chunk
+	const uint64_t nch = (in_bytes + cin - 1) / cin;
+	const uint64_t in_stride = align256(cin + 64), out_stride = align256(pim_snappy_compress_bound(cin, block_size)),
+	               off_stride = align256(cblocks + 1);
+	const double a0 = now_s();
+	const bool ok = grow(d.d_a, d.cap_a, 2 * in_stride) && grow(d.d_b, d.cap_b, 2 * out_stride) &&
+	                grow(d.d_scratch, d.cap_s, pim_snappy_compress_scratch_bytes(cin, block_size)) && grow(d.d_off, d.cap_off, 2 * off_stride) &&
+	                grow_pinned(d.h_pin, d.cap_pin, nch);
+	tm.alloc = now_s() - a0;
+	if (!ok)
+		return SNAPPY_BUFFER_TOO_SMALL;
+	int rc = SNAPPY_OK;
+	uint64_t at = 0; // host offset of the next compressed chunk
+	auto finish = [&](uint64_t i) { // chunk i's size is known once its kernels are done: queue its D2H
+		const int b = (int)(i & 1);
+		if (cudaEventSynchronize(d.ev_k[b]) != cudaSuccess) {
+			rc = SNAPPY_INVALID_INPUT;
+			return;
+		}
+		const uint64_t t = d.h_pin[i];
+		if (i == 0)
+			cudaEventRecord(d.ev_span[4], d.s_out);
+		cudaMemcpyAsync(host_out + at, d.d_b + b * out_stride, t, cudaMemcpyDeviceToHost, d.s_out);
+		cudaEventRecord(d.ev_out[b], d.s_out);
+		at += t;
+	};
+	for (uint64_t i = 0; i < nch && rc == SNAPPY_OK; i++) {
+		const int b = (int)(i & 1);
+		const uint64_t lo = i * cin, bytes = std::min(in_bytes - lo, cin), nb = (bytes + block_size - 1) / block_size;
+		// H2D: the buffer was last read by the kernels of chunk i-2
+		if (i >= 2)
+			cudaStreamWaitEvent(d.s_in, d.ev_k[b], 0);
+		if (i == 0)
+			cudaEventRecord(d.ev_span[0], d.s_in);
+		cudaMemcpyAsync(d.d_a + b * in_stride, host_in + lo, bytes, cudaMemcpyHostToDevice, d.s_in);
+		cudaEventRecord(d.ev_in[b], d.s_in);
+		if (i + 1 == nch)
+			cudaEventRecord(d.ev_span[1], d.s_in);
+		// kernels: the output buffer was last read by the D2H of chunk i-2
+		cudaStreamWaitEvent(d.stream, d.ev_in[b], 0);
+		if (i >= 2)
+			cudaStreamWaitEvent(d.stream, d.ev_out[b], 0);
+		if (i == 0)
+			cudaEventRecord(d.ev_span[2], d.stream);
+		rc = pim_snappy_compress_device(d.d_a + b * in_stride, bytes, block_size, d.d_scratch, d.cap_s, d.d_b + b * out_stride,
+		                                d.d_off + b * off_stride, d.stream);
+		cudaMemcpyAsync(d.h_pin + i, d.d_off + b * off_stride + nb, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.stream);
+		cudaEventRecord(d.ev_k[b], d.stream);
+		if (i + 1 == nch)
+			cudaEventRecord(d.ev_span[3], d.stream);
+		if (i >= 1 && rc == SNAPPY_OK)
+			finish(i - 1);
+	}
+	if (rc == SNAPPY_OK)
+		finish(nch - 1);
+	cudaEventRecord(d.ev_span[5], d.s_out);
+	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(d.stream) == cudaSuccess &&
+	                    cudaStreamSynchronize(d.s_out) == cudaSuccess;
+	if (!synced) {
+		fprintf(stderr, "pim_snappy: compress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+		return SNAPPY_INVALID_INPUT;
+	}
+	if (rc != SNAPPY_OK)
+		return rc;
+	cudaEventElapsedTime(&tm.copy_in, d.ev_span[0], d.ev_span[1]);
+	cudaEventElapsedTime(&tm.run, d.ev_span[2], d.ev_span[3]);
+	cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
+	*total = at;
+	return SNAPPY_OK;
+}
+
+// Decompress blocks [0, nb) of a shard as a stream of chunks.  off[0..nb] are the blocks' offsets
+// in host_comp (off[0] == 0); the output goes to host_out.
+int decompress_shard_streamed(DeviceCtx &d, const uint8_t *host_comp, const uint64_t *off, uint64_t nb, uint32_t block_size,
+                              uint64_t out_bytes, uint8_t *host_out, ShardTimes &tm)
+{
+	const uint64_t cblocks = std::max<uint64_t>(1, chunk_bytes() / block_size);
+	const uint64_t nch = (nb + cblocks - 1) / cblocks;
+	uint64_t max_c = 0; // largest compressed chunk
+	for (uint64_t i = 0; i < nch; i++)
+		max_c = std::max(max_c, off[std::min(nb, (i + 1) * cblocks)] - off[i * cblocks]);
+	const uint64_t out_stride = align256(cblocks * block_size + 64), c_stride = align256(max_c + 64);
+	const double a0 = now_s();
+	const bool ok = grow(d.d_a, d.cap_a, 2 * out_stride) && grow(d.d_b, d.cap_b, 2 * c_stride) && grow(d.d_off, d.cap_off, nb + 1) &&
+	                grow_pinned(d.h_pin, d.cap_pin, nb + 1 + nch) && grow(d.d_statv, d.cap_statv, nch);
+	tm.alloc = now_s() - a0;
+	if (!ok)
+		return SNAPPY_BUFFER_TOO_SMALL;
+	memcpy(d.h_pin, off, (nb + 1) * sizeof(uint64_t));
+	uint32_t *h_stat = reinterpret_cast<uint32_t *>(d.h_pin + nb + 1);
+	int rc = SNAPPY_OK;
+	cudaEventRecord(d.ev_span[0], d.s_in);
+	cudaMemcpyAsync(d.d_off, d.h_pin, (nb + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d.s_in);
+	for (uint64_t i = 0; i < nch && rc == SNAPPY_OK; i++) {
+		const int b = (int)(i & 1);
+		const uint64_t blo = i * cblocks, bhi = std::min(nb, blo + cblocks);
+		const uint64_t c_lo = off[blo], c_bytes = off[bhi] - c_lo;
+		const uint64_t o_lo = blo * (uint64_t)block_size, o_bytes = std::min(out_bytes, bhi * (uint64_t)block_size) - o_lo;
+		if (i >= 2)
+			cudaStreamWaitEvent(d.s_in, d.ev_k[b], 0);
+		cudaMemcpyAsync(d.d_b + b * c_stride, host_comp + c_lo, c_bytes, cudaMemcpyHostToDevice, d.s_in);
+		cudaEventRecord(d.ev_in[b], d.s_in);
+		if (i + 1 == nch)
+			cudaEventRecord(d.ev_span[1], d.s_in);
+		cudaStreamWaitEvent(d.stream, d.ev_in[b], 0);
+		if (i >= 2)
+			cudaStreamWaitEvent(d.stream, d.ev_out[b], 0);
+		if (i == 0)
+			cudaEventRecord(d.ev_span[2], d.stream);
+		// the offsets are relative to the shard; the chunk's bytes start at c_lo
+		rc = pim_snappy_decompress_device(d.d_b + b * c_stride - c_lo, d.d_off + blo, bhi - blo, block_size, o_bytes, d.d_a + b * out_stride,
+		                                  d.d_statv + i, d.stream);
+		cudaEventRecord(d.ev_k[b], d.stream);
+		if (i + 1 == nch)
+			cudaEventRecord(d.ev_span[3], d.stream);
+		cudaStreamWaitEvent(d.s_out, d.ev_k[b], 0);
+		if (i == 0)
+			cudaEventRecord(d.ev_span[4], d.s_out);
+		cudaMemcpyAsync(host_out + o_lo, d.d_a + b * out_stride, o_bytes, cudaMemcpyDeviceToHost, d.s_out);
+		cudaEventRecord(d.ev_out[b], d.s_out);
+	}
+	cudaStreamWaitEvent(d.s_out, d.ev_k[(nch - 1) & 1], 0);
+	cudaMemcpyAsync(h_stat, d.d_statv, nch * sizeof(uint32_t), cudaMemcpyDeviceToHost, d.s_out);
+	cudaEventRecord(d.ev_span[5], d.s_out);
+	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(d.stream) == cudaSuccess &&
+	                    cudaStreamSynchronize(d.s_out) == cudaSuccess;
+	if (!synced) {
+		fprintf(stderr, "pim_snappy: decompress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+		return SNAPPY_INVALID_INPUT;
+	}
+	if (rc != SNAPPY_OK)
+		return rc;
+	for (uint64_t i = 0; i < nch; i++)
+		if (h_stat[i] != 0)
+			return SNAPPY_INVALID_INPUT;
+	cudaEventElapsedTime(&tm.copy_in, d.ev_span[0], d.ev_span[1]);
+	cudaEventElapsedTime(&tm.run, d.ev_span[2], d.ev_span[3]);
+	cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
+	return SNAPPY_OK;
 }
 
 } // namespace
@@ -309,6 +510,7 @@ extern "C" int pim_snappy_set_devices(const int *device_ids, int n)
 }
 
 extern "C" int pim_snappy_device_count(void) { return ensure_devices(); }
+extern "C" void pim_snappy_set_chunk_bytes(uint64_t bytes) { g_chunk_bytes.store(bytes == ~uint64_t(0) ? bytes - 1 : bytes); }
 
 // ----------------------------------------------------------------------- setup
 
@@ -398,6 +600,23 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 	std::vector<ShardTimes> tm(ng);
 	std::vector<uint64_t> total(ng, 0);
 	std::vector<int> rc(ng, SNAPPY_OK);
+
+	// One device, a shard of several chunks and room for the worst case: stream the chunks
+	// (copies overlap the kernels, compressed chunks go straight to their final place).
+	if (ng == 1 && chunk_bytes() && len > 2 * chunk_bytes() && hlen + pim_snappy_compress_bound(len, block_size) <= cap) {
+		DeviceCtx &d = g_devs[0];
+		cudaSetDevice(d.dev);
+		const int r = compress_shard_streamed(d, input->buffer, len, block_size, output->buffer + hlen, &total[0], tm[0]);
+		if (r != SNAPPY_OK)
+			return (snappy_status)r;
+		runtime->d_alloc = tm[0].alloc;
+		runtime->copy_in = tm[0].copy_in * 1e-3;
+		runtime->run = tm[0].run * 1e-3;
+		runtime->copy_out = tm[0].copy_out * 1e-3;
+		output->length = hlen + total[0];
+		output->curr = output->buffer + output->length;
+		return SNAPPY_OK;
+	}
 
 	// phase 1: H2D + kernels + read back each shard's compressed size
 	for_each_shard(ng, [&](int g) {
@@ -544,6 +763,13 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 		const uint64_t o_lo = lo * (uint64_t)block_size;
 		const uint64_t o_bytes = std::min(out_len, hi * (uint64_t)block_size) - o_lo;
 		cudaSetDevice(d.dev);
+		if (chunk_bytes() && o_bytes > 2 * chunk_bytes()) { // stream the shard chunk by chunk
+			std::vector<uint64_t> rel(nb + 1);
+			for (uint64_t i = 0; i <= nb; i++)
+				rel[i] = off[lo + i] - c_lo;
+			rc[g] = decompress_shard_streamed(d, body + c_lo, rel.data(), nb, block_size, o_bytes, output->buffer + o_lo, tm[g]);
+			return;
+		}
 		const double a0 = now_s();
 		bool ok = grow(d.d_a, d.cap_a, o_bytes + 64) && grow(d.d_b, d.cap_b, c_bytes + 64) && grow(d.d_off, d.cap_off, nb + 1);
 		tm[g].alloc = now_s() - a0;

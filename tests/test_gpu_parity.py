@@ -206,6 +206,31 @@ def test_large_roundtrip_properties(P):
     assert int(d_off[-1].item()) == total and int(d_out[:total].to(torch.int64).sum().item()) == chk1
 
 
+def test_streamed_host_path_matches_single_shot(P, oracle):
+    """The chunked pipeline of the host entry points (H2D | kernels | D2H overlapped) must give the
+    same bytes as one-piece processing and as the oracle, for ragged chunk/block combinations."""
+    data = P.synth_host(P.SYNTH_MIX, 0xC0FFEE, (5 << 20) + 12345)
+    try:
+        for bs, chunk in ((32768, 1 << 20), (4096, 1 << 20), (65536, 3 << 19), (1000, 1 << 20)):
+            want = oracle.compress(data, bs)
+            P.set_chunk_bytes(0)
+            one = P.compress(data, bs)
+            P.set_chunk_bytes(chunk)
+            got = P.compress(data, bs)
+            assert got.size == want.size and np.array_equal(got, want), (bs, chunk)
+            assert np.array_equal(one, want)
+            assert np.array_equal(P.decompress(want), data), (bs, chunk)
+        # a malformed block in a late chunk is still reported
+        bad = oracle.compress(data, 32768).copy()
+        _, _, _, off = P.block_offsets(bad)
+        hdr = bad.size - int(off[-1])
+        bad[hdr + int(off[-3]) + 4] = 0xFF  # copy4 tag with a wild offset at the start of a late block
+        with pytest.raises(P.SnappyError):
+            P.decompress(bad)
+    finally:
+        P.set_chunk_bytes(128 << 20)
+
+
 def test_cli_matches_reference_contract(P, golden, tmp_path):
     # same lines the reference CLI prints (dpu_snappy.c:152,159,212-227), same round trip as `make test`
     cli = os.path.join(os.path.dirname(P.LIB_PATH), "dpu_snappy")
