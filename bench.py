@@ -283,8 +283,17 @@ def run_ours(args):
         kern[k] = {"ms_per_launch": ms, "uncompressed_gbps": n / (ms * 1e-3) / 1e9, "achieved_gbps": alg / (ms * 1e-3) / 1e9,
                    "frac_of_hbm_peak": alg / (ms * 1e-3) / 1e9 / peak, "launches": prof[k]["launches"]}
     dom = max(("compress", "decompress"), key=lambda k: prof[k]["ms"])
+    traffic = None  # DRAM bytes per launch, scaled from the committed ncu --set full capture (profiles/traffic.json)
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            tj = json.load(f)
+        if args.block_size == 32768:
+            tk = tj[f"snappy_{dom}_kernel"]
+            traffic = (tk["dram_read"] + tk["dram_write"]) * n / tj["capture_input_bytes"]
+    except Exception:
+        traffic = None
     roofline = {"kernel": f"snappy_{dom}_kernel", "bound": "hbm", "achieved": kern[dom]["achieved_gbps"], "peak": peak,
-                "unit": "GB/s", "frac": kern[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                "unit": "GB/s", "frac": kern[dom]["frac_of_hbm_peak"], "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": n + comp_bytes / S,
                 "share_of_step": prof[dom]["ms"] / (e0.elapsed_time(e1))}
 

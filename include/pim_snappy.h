@@ -107,6 +107,13 @@ void pim_snappy_host_free(void *p);
 int pim_snappy_set_devices(const int *device_ids, int n);
 int pim_snappy_device_count(void);
 
+/* The contiguous block range [*block_lo, *block_hi) that shard `shard` of
+ * `n_shards` codes: ceil(nblocks / n_shards) blocks each, the last ones
+ * possibly fewer or none (snappy_compress.c:495, snappy_decompress.c:307).  The
+ * entry points use it with one shard per GPU; multi-process callers (one
+ * process per GPU) use it to pick their rank's blocks.  Pure arithmetic. */
+void pim_snappy_shard_range(uint64_t nblocks, int n_shards, int shard, uint64_t *block_lo, uint64_t *block_hi);
+
 /* The host entry points stream shards larger than two chunks: chunk i+1 is
  * copied to the device while chunk i is coded and chunk i-1 is copied back
  * (what the reference's separate copy_in / run / copy_out phases,

@@ -31,6 +31,7 @@ from .api import (  # noqa: F401
     synth_device,
     set_devices,
     set_chunk_bytes,
+    shard_range,
     device_count,
     launch_count,
     profile,

@@ -510,6 +510,14 @@ extern "C" int pim_snappy_set_devices(const int *device_ids, int n)
 }
 
 extern "C" int pim_snappy_device_count(void) { return ensure_devices(); }
+extern "C" void pim_snappy_shard_range(uint64_t nblocks, int n_shards, int shard, uint64_t *block_lo, uint64_t *block_hi)
+{
+	if (n_shards <= 0 || shard < 0 || shard >= n_shards) {
+		*block_lo = *block_hi = 0;
+		return;
+	}
+	shard_range(nblocks, n_shards, shard, block_lo, block_hi);
+}
 extern "C" void pim_snappy_set_chunk_bytes(uint64_t bytes) { g_chunk_bytes.store(bytes == ~uint64_t(0) ? bytes - 1 : bytes); }
 
 // ----------------------------------------------------------------------- setup
