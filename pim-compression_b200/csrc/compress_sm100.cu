@@ -6,10 +6,10 @@
 // multiplicative hash (:161-166), same per-block table sizing (:139-146), same skip heuristic
 // (:333-348), same order of table updates (:391-397), same element encodings (:202-272).
 //
-// One CTA (one warp) per input block.  The block is staged into shared memory with cp.async and
-// the 16-bit hash table lives next to it; the parse itself (compress_warp.cuh) fuses the
+// One CTA (two warps) per input block.  The block is staged into shared memory with cp.async and
+// the 16-bit hash table lives next to it; the parser warp (compress_warp.cuh) fuses the
 // reference's step 1 / step 3 probes into 32-lane passes that resolve several (literal, copy)
-// pairs per shared-memory round trip.
+// pairs per shared-memory round trip, the emitter warp turns its per-pass records into bytes.
 // Each block writes to a fixed worst-case slot; block sizes then go through a device
 // exclusive scan, and a compaction kernel moves every block to its final offset, yielding
 // the contiguous ( u32 size | elements )* stream of the file format.
@@ -29,14 +29,15 @@ __host__ __device__ inline uint32_t slot_stride(uint32_t block_size)
 
 __host__ __device__ inline uint32_t compress_smem_bytes(uint32_t block_size)
 {
-	return 2u * table_entries(block_size) + 16u + block_size + 48u;
+	return 2u * table_entries(block_size) + 16u + ((block_size + 48u + 15u) & ~15u) + (uint32_t)sizeof(EmitRing);
 }
 
-__global__ void __launch_bounds__(32) snappy_compress_kernel(const uint8_t *__restrict__ in, uint64_t in_len, uint32_t block_size,
+__global__ void __launch_bounds__(64) snappy_compress_kernel(const uint8_t *__restrict__ in, uint64_t in_len, uint32_t block_size,
                                                              uint8_t *__restrict__ slots, uint32_t stride, uint32_t *__restrict__ sizes)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
 	const int lane = lane_id();
+	const int tid = threadIdx.x;
 	const uint64_t blk = blockIdx.x;
 	const uint64_t in_off = blk * (uint64_t)block_size;
 	const uint32_t n = (uint32_t)min((uint64_t)block_size, in_len - in_off);
@@ -53,16 +54,26 @@ __global__ void __launch_bounds__(32) snappy_compress_kernel(const uint8_t *__re
 	c.out = slots + blk * (uint64_t)stride;
 	c.n = n;
 
-	stage_bytes_async(sm + 2u * ts_max + c.mis, gsrc, n, lane, 32);
-	cp_async_commit();
-	for (uint32_t i = lane * 16u; i < 2u * ts; i += 512u)
-		*reinterpret_cast<uint4 *>(sm + i) = make_uint4(0, 0, 0, 0);
-	cp_async_wait<0>();
-	__syncwarp();
+	EmitRing *ring = reinterpret_cast<EmitRing *>(sm + 2u * ts_max + 16u + ((block_size + 48u + 15u) & ~15u));
 
-	const uint32_t o = compress_block_warp(c);
-	if (lane == 0)
-		sizes[blk] = o;
+	stage_bytes_async(sm + 2u * ts_max + c.mis, gsrc, n, tid, 64);
+	cp_async_commit();
+	for (uint32_t i = tid * 16u; i < 2u * ts; i += 1024u)
+		*reinterpret_cast<uint4 *>(sm + i) = make_uint4(0, 0, 0, 0);
+	if (tid == 0) {
+		ring->head = 0;
+		ring->tail = 0;
+	}
+	cp_async_wait<0>();
+	__syncthreads();
+
+	if (tid < 32) { // parser warp: the block's serial chain
+		parse_block_warp(c, ring);
+	} else { // emitter warp: output bytes only
+		const uint32_t o = emit_block_warp(c, ring);
+		if (lane == 0)
+			sizes[blk] = o;
+	}
 }
 
 // Exclusive scan of the per-block sizes into 64-bit offsets (one CTA; nblocks is at most a few
@@ -169,7 +180,7 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 		configured_for[dev] = 1;
 	}
 	prof_begin(0, st);
-	snappy_compress_kernel<<<(unsigned)nb, 32, smem, st>>>(d_in, input_len, block_size, slots, stride, sizes);
+	snappy_compress_kernel<<<(unsigned)nb, 64, smem, st>>>(d_in, input_len, block_size, slots, stride, sizes);
 	prof_end(0, st);
 	prof_begin(1, st);
 	scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, nb, d_block_off);

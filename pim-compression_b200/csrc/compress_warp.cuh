@@ -23,10 +23,11 @@
 // In a dense pass (all lanes at consecutive positions) the warp then resolves SEVERAL
 // (literal, copy) pairs without touching shared memory again: first hit lane f, match length m
 // -> the next pair's insert-only lane is f+m-1, its continuation probe f+m, its probes follow;
-// lanes inside the match are skipped (never inserted).  All literals and copy tags found that
-// way are written by one batched emission (prefix sums over ballot masks), and one table
-// update (last writer per slot wins) closes the pass.  Matches of 16 bytes or more are extended
-// by the whole warp (16 bytes per lane per step).
+// lanes inside the match are skipped (never inserted).  One table update (last writer per slot
+// wins) closes the pass.  Matches of 16 bytes or more are extended by the whole warp (16 bytes
+// per lane per step).  All literals and copy tags found in a pass are written by one batched
+// emission (prefix sums over ballot masks) -- by a SECOND warp, fed through a ring of per-pass
+// records in shared memory, so that emission is off the parser's dependency chain.
 //
 // This header is written against warp_prims.cuh so that the identical source also runs on the
 // host lock-step emulator (tests/emu) against the oracle.
@@ -323,8 +324,121 @@ PW_FN void walk_serial(const CBlock &c, Walk &w, bool has_ic, bool valid, uint32
 
 } // namespace cw
 
-// Compress one block with the calling warp.  Returns the bytes written to c.out (4 + elements).
-PW_FN uint32_t compress_block_warp(const CBlock &c)
+// ---------------------------------------------------------------------------------------------
+// Two warps per block.  The PARSER warp runs the passes (probe, walk, table update): that is the
+// block's serial dependency chain.  Everything that only produces output bytes is handed to the
+// EMITTER warp through a small ring of per-pass records in shared memory, so it leaves the chain.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t CW_RING = 4; // records in flight between the two warps
+
+struct EmitRec {
+	uint32_t lanew[32]; // per lane: first byte at its position | match length << 8 | copy offset << 16
+	uint32_t L;         // in-window literal bytes
+	uint32_t H;         // hit lanes
+	uint32_t V;         // insert lanes
+	uint32_t satbit;    // hit lane whose copy is not written from lanew (long match), else 0
+	uint32_t lit_from, lit_len;   // literal emitted before the window's elements (len 0: none)
+	uint32_t copy_off, copy_len;  // copy emitted after them (len 0: none)
+	uint32_t done;      // last record of the block
+	uint32_t pad[7];
+};
+
+struct EmitRing {
+	EmitRec rec[CW_RING];
+	volatile uint32_t head; // records published by the parser
+	volatile uint32_t tail; // records consumed by the emitter
+};
+
+PW_FN void ring_push(EmitRing *ring, uint32_t &head, uint32_t lanew, uint32_t L, uint32_t H, uint32_t V, uint32_t satbit, uint32_t lit_from,
+                     uint32_t lit_len, uint32_t copy_off, uint32_t copy_len, uint32_t done, int lane)
+{
+	while (head - ring->tail >= CW_RING)
+		wp::spin_pause();
+	EmitRec &r = ring->rec[head % CW_RING];
+	r.lanew[lane] = lanew;
+	if (lane == 0) {
+		r.L = L;
+		r.H = H;
+		r.V = V;
+		r.satbit = satbit;
+		r.lit_from = lit_from;
+		r.lit_len = lit_len;
+		r.copy_off = copy_off;
+		r.copy_len = copy_len;
+		r.done = done;
+	}
+	wp::fence_block();
+	wp::syncwarp();
+	head++;
+	if (lane == 0)
+		ring->head = head;
+}
+
+// Emitter warp: turns the parser's records into output bytes.  Returns the bytes written (4 + elements).
+PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring)
+{
+	using namespace cw;
+	const int lane = wp::lane();
+	const uint32_t mybit = 1u << lane;
+	const uint32_t lt = mybit - 1u;
+	const uint32_t le = lt | mybit;
+	uint32_t o = 4; // output cursor (4 bytes reserved for the size, :291)
+	for (uint32_t tail = 0;; tail++) {
+		while (ring->head == tail)
+			wp::spin_pause();
+		wp::fence_block();
+		const EmitRec &r = ring->rec[tail % CW_RING];
+		const uint32_t lanew = r.lanew[lane];
+		const uint32_t L = r.L, H = r.H, V = r.V, satbit = r.satbit, lit_from = r.lit_from, lit_len = r.lit_len, copy_off = r.copy_off,
+		               copy_len = r.copy_len, done = r.done;
+		wp::syncwarp();
+		if (lane == 0)
+			ring->tail = tail + 1; // the slot may be reused
+		if (lit_len) // :355 / :405-409
+			o = emit_literal(c, o, lit_from, lit_len, lane);
+		const uint32_t LS = L & (V << 1); // first byte of each in-window literal
+		const uint32_t Hb = H & ~satbit;  // hit lanes whose tag is written here
+		if (L | Hb) {
+			const uint32_t mlen = (lanew >> 8) & 0xFFu, off = lanew >> 16;
+			const bool inHb = (Hb >> lane) & 1u;
+			const bool three = inHb && !(mlen < 12 && off < 2048);
+			const uint32_t H3 = wp::ballot(three);
+			const uint32_t pre = wp::popc32((L | Hb) & lt) + wp::popc32((LS & le) | (Hb & lt)) + wp::popc32(H3 & lt);
+			uint8_t *dst = c.out + o + pre;
+			if ((L >> lane) & 1u) {
+				dst[0] = (uint8_t)lanew;
+			} else if ((H >> lane) & 1u) {
+				const uint32_t vlow = V & lt;
+				if (vlow) { // literal header: the literal runs from behind the pair's insert lane to me
+					const uint32_t litlen = (uint32_t)lane - 1u - (uint32_t)(31 - wp::clz32(vlow));
+					if (litlen)
+						dst[-(int)litlen - 1] = (uint8_t)((litlen - 1) << 2);
+				}
+				if (inHb) {
+					if (!three) { // :238-240
+						dst[0] = (uint8_t)(1 + ((mlen - 4) << 2) + ((off >> 8) << 5));
+						dst[1] = (uint8_t)off;
+					} else { // :242-244
+						dst[0] = (uint8_t)(2 + ((mlen - 1) << 2));
+						dst[1] = (uint8_t)off;
+						dst[2] = (uint8_t)(off >> 8);
+					}
+				}
+			}
+			o += wp::popc32(L | Hb) + wp::popc32(LS | Hb) + wp::popc32(H3);
+		}
+		if (copy_len)
+			o = emit_copy(c, o, copy_off, copy_len, lane);
+		if (done)
+			break;
+	}
+	if (lane < 4) // :411
+		c.out[lane] = (uint8_t)((o - 4) >> (8 * lane));
+	return o;
+}
+
+// Parser warp: runs the passes of one block and publishes one record per pass.
+PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 {
 	using namespace cw;
 	const int lane = wp::lane();
@@ -332,8 +446,8 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 	const uint32_t lt = mybit - 1u;
 	const uint32_t le = lt | mybit;
 	const uint32_t n = c.n;
-	uint32_t o = 4;    // output cursor (4 bytes reserved for the size, :291)
 	uint32_t emit = 0; // first input byte not yet emitted (next_emit)
+	uint32_t head = 0; // records published so far
 
 	if (n >= CW_MARGIN) {
 		const uint32_t limit = n - CW_MARGIN;
@@ -452,50 +566,22 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 				pos_last = wp::reduce_max(mybit == sel ? p + add : 0u);
 			}
 
-			// ---- emission --------------------------------------------------------------------
+			// ---- hand the pass's output to the emitter warp -------------------------------------
+			uint32_t lit_from = 0, lit_len = 0, copy_off = 0, copy_len = 0;
 			if (!has_ic && w.firstbit) { // the first pair's literal started before this window
 				const uint32_t lit_to = wp::reduce_max(mybit == w.firstbit ? p : 0u);
-				o = emit_literal(c, o, emit, lit_to - emit, lane);
+				lit_from = emit;
+				lit_len = lit_to - emit;
 			}
 			const uint32_t before_last = w.lastbit ? w.lastbit - 1u : 0u;
 			const uint32_t first_region = has_ic ? 0u : w.firstbit - 1u; // (firstbit == 0: nothing is emitted anyway)
 			const uint32_t L = Imask & ~w.H & ~w.V & ~first_region & before_last; // in-window literal bytes
-			const uint32_t LS = L & (w.V << 1);                                   // first byte of each such literal
-			const uint32_t Hb = w.H & ~w.satbit;                                  // hit lanes whose tag is written here
-			const uint32_t off = p - cand;
-			const bool inHb = (Hb >> lane) & 1u;
-			const bool three = inHb && !(mlen < 12 && off < 2048);
-			const uint32_t H3 = wp::ballot(three);
-			if (L | Hb) {
-				const uint32_t pre = wp::popc32((L | Hb) & lt) + wp::popc32((LS & le) | (Hb & lt)) + wp::popc32(H3 & lt);
-				uint8_t *dst = c.out + o + pre;
-				if ((L >> lane) & 1u) {
-					dst[0] = (uint8_t)cur[0];
-				} else if ((w.H >> lane) & 1u) {
-					const uint32_t vlow = w.V & lt;
-					if (vlow) { // literal header: the literal runs from behind the pair's insert lane to me
-						const uint32_t litlen = (uint32_t)lane - 1u - (uint32_t)(31 - wp::clz32(vlow));
-						if (litlen)
-							dst[-(int)litlen - 1] = (uint8_t)((litlen - 1) << 2);
-					}
-					if (inHb) {
-						if (!three) { // :238-240
-							dst[0] = (uint8_t)(1 + ((mlen - 4) << 2) + ((off >> 8) << 5));
-							dst[1] = (uint8_t)off;
-						} else { // :242-244
-							dst[0] = (uint8_t)(2 + ((mlen - 1) << 2));
-							dst[1] = (uint8_t)off;
-							dst[2] = (uint8_t)(off >> 8);
-						}
-					}
-				}
-				o += wp::popc32(L | Hb) + wp::popc32(LS | Hb) + wp::popc32(H3);
-			}
 			int outcome = w.outcome;
 			if (outcome == 3) { // match of >= 16 bytes: extend with the whole warp
 				const uint32_t cf = wp::reduce_max(mybit == w.satbit ? cand : 0u);
 				const uint32_t total = 16u + match_length(c, cf + 16, pos_last + 16, n - pos_last - 16, lane);
-				o = emit_copy(c, o, pos_last - cf, total, lane);
+				copy_off = pos_last - cf;
+				copy_len = total;
 				q = pos_last + total;
 				emit = q;
 				outcome = 0;
@@ -503,6 +589,9 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 				q = pos_last;
 				emit = q;
 			}
+			if (L | w.H | lit_len)
+				ring_push(ring, head, (cur[0] & 0xFFu) | (mlen << 8) | ((p - cand) << 16), L, w.H, w.V, w.satbit, lit_from, lit_len, copy_off,
+				          copy_len, 0u, lane);
 			wp::syncwarp(); // table writes visible to the next pass
 
 			if (outcome == 2)
@@ -519,11 +608,8 @@ PW_FN uint32_t compress_block_warp(const CBlock &c)
 			}
 		}
 	}
-	if (emit < n) // :405-409
-		o = cw::emit_literal(c, o, emit, n - emit, lane);
-	if (lane < 4) // :411
-		c.out[lane] = (uint8_t)((o - 4) >> (8 * lane));
-	return o;
+	// the rest of the block is one literal (:405-409); this record also ends the block
+	ring_push(ring, head, 0u, 0u, 0u, 0u, 0u, emit, n - emit, 0u, 0u, 1u, lane);
 }
 
 } // namespace pimsnappy

@@ -21,6 +21,8 @@ uint32_t shfl(uint32_t v, int src_lane);
 uint32_t match_any(uint32_t v);
 uint32_t reduce_max(uint32_t v);
 void syncwarp();
+void spin_pause();  // inside a wait loop on shared memory written by another warp
+inline void fence_block() {}
 inline uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
 {
 	sh &= 31u;
@@ -44,6 +46,8 @@ __device__ __forceinline__ uint32_t shfl(uint32_t v, int src_lane) { return __sh
 __device__ __forceinline__ uint32_t match_any(uint32_t v) { return __match_any_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ uint32_t reduce_max(uint32_t v) { return __reduce_max_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ void syncwarp() { __syncwarp(); }
+__device__ __forceinline__ void spin_pause() { __nanosleep(20); }
+__device__ __forceinline__ void fence_block() { __threadfence_block(); }
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) { return __funnelshift_r(lo, hi, sh); }
 __device__ __forceinline__ int ffs32(uint32_t v) { return __ffs((int)v); }
 __device__ __forceinline__ int clz32(uint32_t v) { return __clz((int)v); }

@@ -33,44 +33,64 @@ extern "C" void emu_stats(unsigned long out[8], int reset)
 
 namespace {
 
-constexpr int NL = 32;
+constexpr int NL = 32;  // lanes per warp
+constexpr int NW = 2;   // warps: 0 parser, 1 emitter
+constexpr int NC = NL * NW;
 constexpr size_t STACK = 256 * 1024;
 
-ucontext_t g_main, g_ctx[NL];
+ucontext_t g_main, g_ctx[NC];
 int g_cur = 0;
-bool g_done[NL];
-uint32_t g_slot[NL];
-int g_op[NL];          // which primitive each lane is in (divergence check)
-unsigned g_opseq[NL];  // how many primitives each lane has executed
+bool g_done[NC];
+uint32_t g_slot[NC];
+int g_op[NC];          // which primitive each lane is in (divergence check)
+unsigned g_opseq[NC];  // how many primitives each lane has executed
 int g_order = 0; // 0: lanes run 0..31 between primitives (lane 31's store wins a conflict), 1: 31..0, 2: shuffled
 void (*g_body)(void *) = nullptr;
 void *g_arg = nullptr;
 
 void yield() { swapcontext(&g_ctx[g_cur], &g_main); }
 
-void check_converged(int op)
-{
-	for (int l = 0; l < NL; l++) {
-		if (g_done[l] || g_op[l] != op || g_opseq[l] != g_opseq[g_cur]) {
-			fprintf(stderr, "warp_emu: lanes diverged at a warp primitive (lane %d op %d seq %u vs lane %d op %d seq %u%s)\n", g_cur, op,
-			        g_opseq[g_cur], l, g_op[l], g_opseq[l], g_done[l] ? ", finished" : "");
-			abort();
-		}
-	}
-}
+// Publish v, wait until every lane of the warp has published for the same primitive, combine.
+// Lanes may arrive rounds apart (a wait loop on another warp's flag lets them leave at different
+// times, as on the GPU, where they reconverge at the next primitive).  Slots are double-buffered
+// by the parity of the primitive's sequence number: a lane can only overwrite a slot two
+// primitives later, which needs every lane to have published the next one, i.e. to be done
+// reading this one.
+uint32_t g_slot2[2][NC];
+int g_op2[2][NC];
 
-// publish v, wait for everyone, return after everyone has read
 template <class F>
 uint32_t exchange(int op, uint32_t v, F &&combine)
 {
-	g_slot[g_cur] = v;
-	g_op[g_cur] = op;
-	g_opseq[g_cur]++;
-	yield(); // every lane has published
-	check_converged(op);
-	const uint32_t r = combine();
-	yield(); // every lane has read
-	return r;
+	const unsigned seq = ++g_opseq[g_cur];
+	const int par = seq & 1;
+	g_slot2[par][g_cur] = v;
+	g_op2[par][g_cur] = op;
+	const int w0 = (g_cur / NL) * NL;
+	for (;;) {
+		bool all = true;
+		for (int l = w0; l < w0 + NL; l++) {
+			if (g_opseq[l] < seq) {
+				if (g_done[l]) {
+					fprintf(stderr, "warp_emu: lane %d finished while lane %d waits at a warp primitive\n", l, g_cur);
+					abort();
+				}
+				all = false;
+			}
+		}
+		if (all)
+			break;
+		yield();
+	}
+	for (int l = w0; l < w0 + NL; l++) {
+		if (g_op2[par][l] != op) {
+			fprintf(stderr, "warp_emu: lanes diverged at a warp primitive (lane %d op %d vs lane %d op %d, seq %u)\n", g_cur, op, l, g_op2[par][l], seq);
+			abort();
+		}
+	}
+	for (int l = 0; l < NL; l++)
+		g_slot[w0 + l] = g_slot2[par][w0 + l]; // combine() reads g_slot of the own warp
+	return combine();
 }
 
 void trampoline()
@@ -82,10 +102,10 @@ void trampoline()
 
 void run_warp(void (*body)(void *), void *arg)
 {
-	static std::vector<char> stacks(NL * STACK);
+	static std::vector<char> stacks(NC * STACK);
 	g_body = body;
 	g_arg = arg;
-	for (int l = 0; l < NL; l++) {
+	for (int l = 0; l < NC; l++) {
 		getcontext(&g_ctx[l]);
 		g_ctx[l].uc_stack.ss_sp = stacks.data() + l * STACK;
 		g_ctx[l].uc_stack.ss_size = STACK;
@@ -99,8 +119,8 @@ void run_warp(void (*body)(void *), void *arg)
 		bool any = false;
 		static unsigned rnd = 12345;
 		rnd = rnd * 1664525u + 1013904223u;
-		for (int i = 0; i < NL; i++) {
-			const int l = g_order == 0 ? i : (g_order == 1 ? NL - 1 - i : (int)((i * 13u + (rnd >> 16)) & 31u));
+		for (int i = 0; i < NC; i++) {
+			const int l = g_order == 0 ? i : (g_order == 1 ? NC - 1 - i : (int)((i * 13u + (rnd >> 16)) & (NC - 1)));
 			if (g_done[l])
 				continue;
 			any = true;
@@ -116,27 +136,28 @@ void run_warp(void (*body)(void *), void *arg)
 
 namespace pimsnappy {
 namespace wp {
-int lane() { return g_cur; }
+int lane() { return g_cur % NL; }
+static int wbase() { return (g_cur / NL) * NL; }
 uint32_t ballot(bool pred)
 {
 	return exchange(1, pred ? 1u : 0u, [] {
 		uint32_t m = 0;
 		for (int l = 0; l < NL; l++)
-			m |= (g_slot[l] & 1u) << l;
+			m |= (g_slot[wbase() + l] & 1u) << l;
 		return m;
 	});
 }
 uint32_t shfl(uint32_t v, int src_lane)
 {
 	const int s = src_lane & 31;
-	return exchange(2, v, [s] { return g_slot[s]; });
+	return exchange(2, v, [s] { return g_slot[wbase() + s]; });
 }
 uint32_t match_any(uint32_t v)
 {
 	return exchange(3, v, [v] {
 		uint32_t m = 0;
 		for (int l = 0; l < NL; l++)
-			m |= (g_slot[l] == v ? 1u : 0u) << l;
+			m |= (g_slot[wbase() + l] == v ? 1u : 0u) << l;
 		return m;
 	});
 }
@@ -145,7 +166,7 @@ uint32_t reduce_max(uint32_t v)
 	return exchange(5, v, [] {
 		uint32_t m = 0;
 		for (int l = 0; l < NL; l++)
-			m = g_slot[l] > m ? g_slot[l] : m;
+			m = g_slot[wbase() + l] > m ? g_slot[wbase() + l] : m;
 		return m;
 	});
 }
@@ -153,6 +174,7 @@ void syncwarp()
 {
 	exchange(4, 0, [] { return 0u; });
 }
+void spin_pause() { yield(); }
 } // namespace wp
 } // namespace pimsnappy
 
@@ -160,15 +182,20 @@ namespace {
 
 struct Job {
 	pimsnappy::CBlock blk;
+	pimsnappy::EmitRing ring;
 	uint32_t result;
 };
 
 void body(void *arg)
 {
 	Job *j = static_cast<Job *>(arg);
-	const uint32_t r = pimsnappy::compress_block_warp(j->blk);
-	if (pimsnappy::wp::lane() == 0)
-		j->result = r;
+	if (g_cur < NL) {
+		pimsnappy::parse_block_warp(j->blk, &j->ring);
+	} else {
+		const uint32_t r = pimsnappy::emit_block_warp(j->blk, &j->ring);
+		if (pimsnappy::wp::lane() == 0)
+			j->result = r;
+	}
 }
 
 size_t put_varint(uint8_t *p, uint32_t v) // snappy_compress.c:69-98
@@ -211,6 +238,7 @@ extern "C" uint64_t emu_compress(const uint8_t *in, uint64_t len, uint32_t block
 		j.blk.out = reinterpret_cast<uint8_t *>(slotmem.data());
 		j.blk.n = n;
 		j.result = 0;
+		j.ring.head = j.ring.tail = 0;
 		run_warp(body, &j);
 		memcpy(out + o, j.blk.out, j.result);
 		o += j.result;
