@@ -6,8 +6,10 @@
 // multiplicative hash (:161-166), same per-block table sizing (:139-146), same skip heuristic
 // (:333-348), same order of table updates (:391-397), same element encodings (:202-272).
 //
-// One CTA (two warps) per input block.  The block is staged into shared memory with cp.async and
-// the 16-bit hash table lives next to it; the parser warp (compress_warp.cuh) fuses the
+// One CTA (two warps) per input block.  The 16-bit hash table lives in shared memory (32 KB for
+// blocks of 16 KB and more: six blocks per SM); the input is NOT staged -- it is prefetched into L2
+// and read from there (sequential window via L1), which doubles the blocks in flight compared to
+// keeping table + input in shared memory.  The parser warp (compress_warp.cuh) fuses the
 // reference's step 1 / step 3 probes into 32-lane passes that resolve several (literal, copy)
 // pairs per shared-memory round trip, the emitter warp turns its per-pass records into bytes.
 // Each block writes to a fixed worst-case slot; block sizes then go through a device
@@ -29,11 +31,17 @@ __host__ __device__ inline uint32_t slot_stride(uint32_t block_size)
 
 __host__ __device__ inline uint32_t compress_smem_bytes(uint32_t block_size)
 {
-	return 2u * table_entries(block_size) + 16u + ((block_size + 48u + 15u) & ~15u) + (uint32_t)sizeof(EmitRing);
+	return 2u * table_entries(block_size) + 16u + (uint32_t)sizeof(EmitRing);
 }
 
+// The parse reads up to TAIL_SLACK bytes past a block's end.  Inside the stream that is the next
+// block; the stream's last block is read from a copy in scratch that has the slack behind it.
+constexpr uint32_t TAIL_SLACK = 32;
+__host__ __device__ inline uint64_t tail_copy_bytes(uint32_t block_size) { return ((uint64_t)block_size + TAIL_SLACK + 16u + 255u) & ~255ull; }
+
 __global__ void __launch_bounds__(64) snappy_compress_kernel(const uint8_t *__restrict__ in, uint64_t in_len, uint32_t block_size,
-                                                             uint8_t *__restrict__ slots, uint32_t stride, uint32_t *__restrict__ sizes)
+                                                             const uint8_t *__restrict__ tail_copy, uint8_t *__restrict__ slots, uint32_t stride,
+                                                             uint32_t *__restrict__ sizes)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
 	const int lane = lane_id();
@@ -41,30 +49,28 @@ __global__ void __launch_bounds__(64) snappy_compress_kernel(const uint8_t *__re
 	const uint64_t blk = blockIdx.x;
 	const uint64_t in_off = blk * (uint64_t)block_size;
 	const uint32_t n = (uint32_t)min((uint64_t)block_size, in_len - in_off);
-	const uint8_t *gsrc = in + in_off;
+	const uint8_t *gsrc = blk + 1 == gridDim.x ? tail_copy : in + in_off;
 
 	const uint32_t ts_max = table_entries(block_size);
 	const uint32_t ts = table_entries(n);
 
 	CBlock c;
-	c.inw = reinterpret_cast<const uint32_t *>(sm + 2u * ts_max);
-	c.mis = (uint32_t)(reinterpret_cast<uintptr_t>(gsrc) & 15u);
+	c.mis = (uint32_t)(reinterpret_cast<uintptr_t>(gsrc) & 3u);
+	c.inw = reinterpret_cast<const uint32_t *>(gsrc - c.mis);
 	c.table = reinterpret_cast<uint16_t *>(sm);
 	c.shift = 32 - (31 - __clz(ts)); // snappy_compress.c:288
 	c.out = slots + blk * (uint64_t)stride;
 	c.n = n;
 
-	EmitRing *ring = reinterpret_cast<EmitRing *>(sm + 2u * ts_max + 16u + ((block_size + 48u + 15u) & ~15u));
-
-	stage_bytes_async(sm + 2u * ts_max + c.mis, gsrc, n, tid, 64);
-	cp_async_commit();
+	EmitRing *ring = reinterpret_cast<EmitRing *>(sm + 2u * ts_max + 16u);
+	for (uint32_t i = tid * 128u; i < n; i += 64u * 128u) // HBM -> L2 for the whole block, ahead of the parse
+		asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc + i));
 	for (uint32_t i = tid * 16u; i < 2u * ts; i += 1024u)
 		*reinterpret_cast<uint4 *>(sm + i) = make_uint4(0, 0, 0, 0);
 	if (tid == 0) {
 		ring->head = 0;
 		ring->tail = 0;
 	}
-	cp_async_wait<0>();
 	__syncthreads();
 
 	if (tid < 32) { // parser warp: the block's serial chain
@@ -149,7 +155,7 @@ extern "C" uint64_t pim_snappy_compress_bound(uint64_t input_len, uint32_t block
 extern "C" uint64_t pim_snappy_compress_scratch_bytes(uint64_t input_len, uint32_t block_size)
 {
 	const uint64_t nb = pim_snappy_num_blocks(input_len, block_size);
-	return ((nb * 4 + 255) & ~255ull) + nb * (uint64_t)slot_stride(block_size) + 256;
+	return ((nb * 4 + 255) & ~255ull) + tail_copy_bytes(block_size) + nb * (uint64_t)slot_stride(block_size) + 256;
 }
 
 extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch,
@@ -166,7 +172,12 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 		return SNAPPY_OK;
 	}
 	uint32_t *sizes = reinterpret_cast<uint32_t *>(d_scratch);
-	uint8_t *slots = d_scratch + ((nb * 4 + 255) & ~255ull);
+	uint8_t *tail_copy = d_scratch + ((nb * 4 + 255) & ~255ull);
+	uint8_t *slots = tail_copy + tail_copy_bytes(block_size);
+	// the stream's last block, with readable slack behind it (same 4-byte phase as in the stream)
+	const uint64_t last_off = (nb - 1) * (uint64_t)block_size;
+	tail_copy += reinterpret_cast<uintptr_t>(d_in + last_off) & 15u;
+	PIM_CUDA_TRY(cudaMemcpyAsync(tail_copy, d_in + last_off, input_len - last_off, cudaMemcpyDeviceToDevice, st));
 	const uint32_t stride = slot_stride(block_size);
 	const uint32_t smem = compress_smem_bytes(block_size);
 
@@ -180,7 +191,7 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 		configured_for[dev] = 1;
 	}
 	prof_begin(0, st);
-	snappy_compress_kernel<<<(unsigned)nb, 64, smem, st>>>(d_in, input_len, block_size, slots, stride, sizes);
+	snappy_compress_kernel<<<(unsigned)nb, 64, smem, st>>>(d_in, input_len, block_size, tail_copy, slots, stride, sizes);
 	prof_end(0, st);
 	prof_begin(1, st);
 	scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, nb, d_block_off);

@@ -60,7 +60,7 @@ inline uint32_t cw_table_entries(uint32_t n) // snappy_compress.c:139-146
 }
 
 struct CBlock {
-	const uint32_t *inw; // 4-byte aligned; input byte i is byte (i + mis) from here (shared memory on the device)
+	const uint32_t *inw; // 4-byte aligned; input byte i is byte (i + mis) from here (global memory, L2-resident, on the device)
 	uint32_t mis;        // 0..15; 24 readable bytes follow the input
 	uint16_t *table;     // zeroed, cw_table_entries(n) entries
 	int shift;           // 32 - log2(entries), snappy_compress.c:288
