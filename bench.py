@@ -314,7 +314,10 @@ def run_ours(args):
         h_back = P.PinnedBuffer(n + 4096)
         torch.cuda.synchronize()
 
+        phase = {"compress": 0.0, "decompress": 0.0}
+
         def e2e_stream(s):
+            tp0 = time.perf_counter()
             inp, out, rt = P.HostBufferContext(), P.HostBufferContext(), P.ProgramRuntime()
             inp.buffer = inp.curr = h_in[s % distinct].ptr
             inp.length, inp.max, out.max = n, 2**63, 2**63
@@ -322,6 +325,7 @@ def run_ours(args):
             rc = L.snappy_compress_dpu(C.byref(inp), C.byref(out), bs, C.byref(rt))
             assert rc == 0, f"snappy_compress_dpu rc={rc}"
             clen = int(out.length)
+            tp1 = time.perf_counter()
             # what setup_decompression does, minus its allocation: consume the length varint
             hdr = bytes(h_comp.array[:5])
             k = next(i for i in range(5) if not hdr[i] & 0x80) + 1
@@ -331,12 +335,30 @@ def run_ours(args):
             dout.length, dout.max = n, 2**63
             rc = L.snappy_decompress_dpu(C.byref(dinp), C.byref(dout), C.byref(rt))
             assert rc == 0, f"snappy_decompress_dpu rc={rc}"
+            phase["compress"] += tp1 - tp0
+            phase["decompress"] += time.perf_counter() - tp1
             return clen
 
         for _ in range(max(1, min(args.warmup, 2))):
             clens = [e2e_stream(s) for s in range(S)]
         assert np.array_equal(h_back.array[:n], h_in[(S - 1) % distinct].array), "e2e round trip mismatch"
+        # the link the end-to-end number is bounded by: plain pinned copies of one stream, each direction
+        d_tmp = d_back
+        pcie = {}
+        rtlib = C.CDLL("libcudart.so.12")  # the runtime torch already loaded
+        rtlib.cudaMemcpyAsync.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+        for name, fn in (("h2d", lambda: rtlib.cudaMemcpyAsync(d_tmp.data_ptr(), h_in[0].ptr, n, 4, st)),
+                         ("d2h", lambda: rtlib.cudaMemcpyAsync(h_back.ptr, d_tmp.data_ptr(), n, 4, st))):
+            assert fn() == 0
+            torch.cuda.synchronize()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            assert fn() == 0
+            c1.record()
+            torch.cuda.synchronize()
+            pcie[name + "_gbps"] = n / (c0.elapsed_time(c1) * 1e-3) / 1e9
         sync_all()
+        phase["compress"] = phase["decompress"] = 0.0
         t0 = time.perf_counter()
         for _ in range(args.steps):
             for s in range(S):
@@ -347,6 +369,8 @@ def run_ours(args):
         csum = sum(clens)
         e2e = {"value": total_U / dt / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(U + csum), "d2h_bytes_per_step": int(csum + U),
                "ms_per_step": dt * 1e3, "distinct_host_streams": distinct,
+               "compress_gbps": U * args.steps / phase["compress"] / 1e9, "decompress_gbps": U * args.steps / phase["decompress"] / 1e9,
+               "pinned_copy": pcie,
                "api": "snappy_compress_dpu + snappy_decompress_dpu (C ABI) on page-locked host buffers, one GPU per rank"}
 
     cpu = None

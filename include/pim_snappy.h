@@ -117,7 +117,7 @@ void pim_snappy_shard_range(uint64_t nblocks, int n_shards, int shard, uint64_t 
 /* The host entry points stream shards larger than two chunks: chunk i+1 is
  * copied to the device while chunk i is coded and chunk i-1 is copied back
  * (what the reference's separate copy_in / run / copy_out phases,
- * snappy_compress.c:560-670, become when they overlap).  Default 128 MiB, or
+ * snappy_compress.c:560-670, become when they overlap).  Default 64 MiB, or
  * $PIM_SNAPPY_CHUNK_MIB; 0 processes every shard in one piece. */
 void pim_snappy_set_chunk_bytes(uint64_t bytes);
 

@@ -101,7 +101,8 @@ struct DeviceCtx {
 	uint32_t *d_status = nullptr;
 	uint64_t *h_small = nullptr;                    // pinned: [0] total, [1] status
 	// chunked pipeline (H2D | kernels | D2H on three streams, two buffers each)
-	cudaStream_t s_in = nullptr, s_out = nullptr;
+	cudaStream_t s_in = nullptr, s_out = nullptr, stream2 = nullptr;
+	std::vector<cudaEvent_t> ev_pool;               // per-group events of the streamed paths (untimed)
 	cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
 	cudaEvent_t ev_span[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // first/last of each stream
 	uint64_t *h_pin = nullptr; size_t cap_pin = 0;  // pinned: per-chunk totals / block offsets (entries)
@@ -133,6 +134,8 @@ int init_devices_locked(const int *ids, int n)
 		if (d.h_pin) cudaFreeHost(d.h_pin);
 		if (d.s_in) cudaStreamDestroy(d.s_in);
 		if (d.s_out) cudaStreamDestroy(d.s_out);
+		if (d.stream2) cudaStreamDestroy(d.stream2);
+		for (auto &e : d.ev_pool) if (e) cudaEventDestroy(e);
 		for (auto &e : d.ev_in) if (e) cudaEventDestroy(e);
 		for (auto &e : d.ev_k) if (e) cudaEventDestroy(e);
 		for (auto &e : d.ev_out) if (e) cudaEventDestroy(e);
@@ -166,6 +169,7 @@ int init_devices_locked(const int *ids, int n)
 		for (auto &e : d.ev) cudaEventCreate(&e);
 		if (cudaStreamCreateWithFlags(&d.s_in, cudaStreamNonBlocking) != cudaSuccess) continue;
 		if (cudaStreamCreateWithFlags(&d.s_out, cudaStreamNonBlocking) != cudaSuccess) continue;
+		if (cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking) != cudaSuccess) continue;
 		for (auto &e : d.ev_in) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
 		for (auto &e : d.ev_k) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
 		for (auto &e : d.ev_out) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
@@ -213,7 +217,7 @@ bool grow_pinned(uint64_t *&p, size_t &cap, size_t need)
 	p = nullptr;
 	cap = 0;
 	need = (need + (need >> 2) + 511) & ~size_t(511);
-	if (cudaHostAlloc(&p, need * sizeof(uint64_t), cudaHostAllocDefault) != cudaSuccess) {
+	if (cudaHostAlloc(&p, need * sizeof(uint64_t), cudaHostAllocMapped) != cudaSuccess) {
 		cudaGetLastError();
 		return false;
 	}
@@ -229,7 +233,7 @@ uint64_t chunk_bytes()
 	uint64_t v = g_chunk_bytes.load(std::memory_order_relaxed);
 	if (v == ~uint64_t(0)) {
 		const char *e = getenv("PIM_SNAPPY_CHUNK_MIB");
-		const long mib = e ? atol(e) : 128;
+		const long mib = e ? atol(e) : 64;
 		v = mib <= 0 ? uint64_t(0) : uint64_t(mib) << 20;
 		g_chunk_bytes.store(v, std::memory_order_relaxed);
 	}
@@ -290,71 +294,111 @@ void for_each_shard(int ng, F &&fn)
 
 inline uint64_t align256(uint64_t v) { return (v + 255) & ~uint64_t(255); }
 
-// Compress one shard (a whole number of blocks) as a stream of chunks: H2D of chunk i+1, the
-// kernels of chunk i and the D2H of chunk i-1 run concurrently on three streams.  The compressed
-// chunks land back to back at host_out.  Returns the shard's compressed bytes in *total.
+// ---- streamed shards ---------------------------------------------------------------------------
+// A shard larger than two chunks is processed as a sequence of block GROUPS with the whole shard
+// resident on the device (streams are < 4 GiB by format): the H2D copies of all groups are queued
+// up front and run ahead, each group's kernels start as soon as its bytes have arrived, and its
+// result goes back to the host as soon as its kernels are done.  Group sizes ramp up from
+// chunk/8 (short pipeline fill) to the chunk size and, for compression, back down (short drain).
+
+cudaEvent_t pool_event(DeviceCtx &d, size_t i)
+{
+	while (d.ev_pool.size() <= i) {
+		cudaEvent_t e = nullptr;
+		cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+		d.ev_pool.push_back(e);
+	}
+	return d.ev_pool[i];
+}
+
+// Group sizes (in units) for `total` units with groups of at most `chunk` units.
+std::vector<uint64_t> plan_groups(uint64_t total, uint64_t chunk, bool ramp_down)
+{
+	std::vector<uint64_t> g;
+	const uint64_t small = std::max<uint64_t>(1, chunk / 8);
+	uint64_t left = total, next = small;
+	const uint64_t tail = ramp_down ? chunk : 0; // units kept for the ramp down
+	while (left > tail) {
+		const uint64_t take = std::min(next, left - tail);
+		g.push_back(take);
+		left -= take;
+		next = std::min(chunk, next * 2);
+	}
+	while (left) { // halves, down to chunk/8
+		const uint64_t take = left <= small ? left : std::max(small, left / 2);
+		g.push_back(take);
+		left -= take;
+	}
+	return g;
+}
+
+// Compress one shard (a whole number of blocks).  The compressed groups land back to back at
+// host_out.  Returns the shard's compressed bytes in *total.
 int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_bytes, uint32_t block_size, uint8_t *host_out,
                             uint64_t *total, ShardTimes &tm)
 {
+	const uint64_t nblocks = (in_bytes + block_size - 1) / block_size;
 	const uint64_t cblocks = std::max<uint64_t>(1, chunk_bytes() / block_size);
-	const uint64_t cin = cblocks * block_size; // input bytes per chunk
-	const uint64_t nch = (in_bytes + cin - 1) / cin;
-	const uint64_t in_stride = align256(cin + 64), out_stride = align256(pim_snappy_compress_bound(cin, block_size)),
-	               off_stride = align256(cblocks + 1);
+	const std::vector<uint64_t> groups = plan_groups(nblocks, cblocks, true);
+	const uint64_t ng = groups.size();
+	const uint64_t gmax = *std::max_element(groups.begin(), groups.end());
+	const uint64_t scratch_stride = align256(pim_snappy_compress_scratch_bytes(gmax * block_size, block_size));
+	// group g: blocks [blo[g], blo[g+1]), compacted output at d_b + out_at[g], offsets at d_off + off_at[g]
+	std::vector<uint64_t> blo(ng + 1, 0), out_at(ng + 1, 0), off_at(ng + 1, 0);
+	for (uint64_t g = 0; g < ng; g++) {
+		blo[g + 1] = blo[g] + groups[g];
+		out_at[g + 1] = out_at[g] + align256(pim_snappy_compress_bound(groups[g] * block_size, block_size));
+		off_at[g + 1] = off_at[g] + groups[g] + 1;
+	}
 	const double a0 = now_s();
-	const bool ok = grow(d.d_a, d.cap_a, 2 * in_stride) && grow(d.d_b, d.cap_b, 2 * out_stride) &&
-	                grow(d.d_scratch, d.cap_s, pim_snappy_compress_scratch_bytes(cin, block_size)) && grow(d.d_off, d.cap_off, 2 * off_stride) &&
-	                grow_pinned(d.h_pin, d.cap_pin, nch);
+	const bool ok = grow(d.d_a, d.cap_a, in_bytes + 64) && grow(d.d_b, d.cap_b, out_at[ng]) && grow(d.d_scratch, d.cap_s, 2 * scratch_stride) &&
+	                grow(d.d_off, d.cap_off, off_at[ng]) && grow_pinned(d.h_pin, d.cap_pin, ng);
 	tm.alloc = now_s() - a0;
 	if (!ok)
 		return SNAPPY_BUFFER_TOO_SMALL;
+	// all H2D copies, queued now; event g: group g has arrived
+	cudaEventRecord(d.ev_span[0], d.s_in);
+	for (uint64_t g = 0; g < ng; g++) {
+		const uint64_t lo = blo[g] * block_size, bytes = std::min(in_bytes, blo[g + 1] * block_size) - lo;
+		cudaMemcpyAsync(d.d_a + lo, host_in + lo, bytes, cudaMemcpyHostToDevice, d.s_in);
+		cudaEventRecord(pool_event(d, g), d.s_in);
+	}
+	cudaEventRecord(d.ev_span[1], d.s_in);
+	// the two compute streams alternate, so that the tail of one group's kernel overlaps the next group
+	cudaStream_t cs[2] = {d.stream, d.stream2};
 	int rc = SNAPPY_OK;
-	uint64_t at = 0; // host offset of the next compressed chunk
-	auto finish = [&](uint64_t i) { // chunk i's size is known once its kernels are done: queue its D2H
-		const int b = (int)(i & 1);
-		if (cudaEventSynchronize(d.ev_k[b]) != cudaSuccess) {
+	uint64_t at = 0; // host offset of the next compressed group
+	auto finish = [&](uint64_t g) { // group g's size is known once its kernels are done: queue its D2H
+		if (cudaEventSynchronize(pool_event(d, ng + g)) != cudaSuccess) {
 			rc = SNAPPY_INVALID_INPUT;
 			return;
 		}
-		const uint64_t t = d.h_pin[i];
-		if (i == 0)
+		const uint64_t t = d.h_pin[g];
+		if (g == 0)
 			cudaEventRecord(d.ev_span[4], d.s_out);
-		cudaMemcpyAsync(host_out + at, d.d_b + b * out_stride, t, cudaMemcpyDeviceToHost, d.s_out);
-		cudaEventRecord(d.ev_out[b], d.s_out);
+		cudaMemcpyAsync(host_out + at, d.d_b + out_at[g], t, cudaMemcpyDeviceToHost, d.s_out);
 		at += t;
 	};
-	for (uint64_t i = 0; i < nch && rc == SNAPPY_OK; i++) {
-		const int b = (int)(i & 1);
-		const uint64_t lo = i * cin, bytes = std::min(in_bytes - lo, cin), nb = (bytes + block_size - 1) / block_size;
-		// H2D: the buffer was last read by the kernels of chunk i-2
-		if (i >= 2)
-			cudaStreamWaitEvent(d.s_in, d.ev_k[b], 0);
-		if (i == 0)
-			cudaEventRecord(d.ev_span[0], d.s_in);
-		cudaMemcpyAsync(d.d_a + b * in_stride, host_in + lo, bytes, cudaMemcpyHostToDevice, d.s_in);
-		cudaEventRecord(d.ev_in[b], d.s_in);
-		if (i + 1 == nch)
-			cudaEventRecord(d.ev_span[1], d.s_in);
-		// kernels: the output buffer was last read by the D2H of chunk i-2
-		cudaStreamWaitEvent(d.stream, d.ev_in[b], 0);
-		if (i >= 2)
-			cudaStreamWaitEvent(d.stream, d.ev_out[b], 0);
-		if (i == 0)
-			cudaEventRecord(d.ev_span[2], d.stream);
-		rc = pim_snappy_compress_device(d.d_a + b * in_stride, bytes, block_size, d.d_scratch, d.cap_s, d.d_b + b * out_stride,
-		                                d.d_off + b * off_stride, d.stream);
-		cudaMemcpyAsync(d.h_pin + i, d.d_off + b * off_stride + nb, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.stream);
-		cudaEventRecord(d.ev_k[b], d.stream);
-		if (i + 1 == nch)
-			cudaEventRecord(d.ev_span[3], d.stream);
-		if (i >= 1 && rc == SNAPPY_OK)
-			finish(i - 1);
+	cudaEventRecord(d.ev_span[2], cs[0]);
+	for (uint64_t g = 0; g < ng && rc == SNAPPY_OK; g++) {
+		cudaStream_t st = cs[g & 1];
+		const uint64_t lo = blo[g] * block_size, bytes = std::min(in_bytes, blo[g + 1] * block_size) - lo;
+		cudaStreamWaitEvent(st, pool_event(d, g), 0);
+		rc = pim_snappy_compress_device(d.d_a + lo, bytes, block_size, d.d_scratch + (g & 1) * scratch_stride, scratch_stride, d.d_b + out_at[g],
+		                                d.d_off + off_at[g], st);
+		cudaMemcpyAsync(d.h_pin + g, d.d_off + off_at[g] + groups[g], sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
+		cudaEventRecord(pool_event(d, ng + g), st);
+		if (g >= 1 && rc == SNAPPY_OK)
+			finish(g - 1);
 	}
 	if (rc == SNAPPY_OK)
-		finish(nch - 1);
+		finish(ng - 1);
 	cudaEventRecord(d.ev_span[5], d.s_out);
-	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(d.stream) == cudaSuccess &&
-	                    cudaStreamSynchronize(d.s_out) == cudaSuccess;
+	// span 3 closes the kernels' interval: after both compute streams
+	cudaStreamWaitEvent(cs[0], pool_event(d, ng + ng - 1), 0);
+	cudaEventRecord(d.ev_span[3], cs[0]);
+	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(cs[0]) == cudaSuccess &&
+	                    cudaStreamSynchronize(cs[1]) == cudaSuccess && cudaStreamSynchronize(d.s_out) == cudaSuccess;
 	if (!synced) {
 		fprintf(stderr, "pim_snappy: compress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
 		return SNAPPY_INVALID_INPUT;
@@ -368,58 +412,93 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 	return SNAPPY_OK;
 }
 
-// Decompress blocks [0, nb) of a shard as a stream of chunks.  off[0..nb] are the blocks' offsets
-// in host_comp (off[0] == 0); the output goes to host_out.
-int decompress_shard_streamed(DeviceCtx &d, const uint8_t *host_comp, const uint64_t *off, uint64_t nb, uint32_t block_size,
-                              uint64_t out_bytes, uint8_t *host_out, ShardTimes &tm)
+// Block offsets of a group travel through mapped pinned memory: one small kernel on the compute
+// stream instead of a copy that would queue behind the bulk H2D transfers.
+__global__ void fetch_offsets_kernel(const uint64_t *__restrict__ host_mapped, uint64_t *__restrict__ d_off, uint64_t n)
 {
-	const uint64_t cblocks = std::max<uint64_t>(1, chunk_bytes() / block_size);
-	const uint64_t nch = (nb + cblocks - 1) / cblocks;
-	uint64_t max_c = 0; // largest compressed chunk
-	for (uint64_t i = 0; i < nch; i++)
-		max_c = std::max(max_c, off[std::min(nb, (i + 1) * cblocks)] - off[i * cblocks]);
-	const uint64_t out_stride = align256(cblocks * block_size + 64), c_stride = align256(max_c + 64);
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+		d_off[i] = host_mapped[i];
+}
+
+// Decompress a whole stream body (nblocks blocks, out_bytes output bytes).  The serial walk over
+// the 4-byte block headers (snappy_decompress.c:317-340) runs on the host WHILE the compressed
+// bytes are uploaded: a group of blocks is launched as soon as the upload has passed its end.
+int decompress_stream_resident(DeviceCtx &d, const uint8_t *body, uint64_t body_len, uint64_t nblocks, uint32_t block_size,
+                               uint64_t out_bytes, uint8_t *host_out, ShardTimes &tm)
+{
+	const std::vector<uint64_t> pieces = plan_groups(body_len, std::max<uint64_t>(chunk_bytes(), 8), false); // compressed bytes
+	const uint64_t np = pieces.size();
 	const double a0 = now_s();
-	const bool ok = grow(d.d_a, d.cap_a, 2 * out_stride) && grow(d.d_b, d.cap_b, 2 * c_stride) && grow(d.d_off, d.cap_off, nb + 1) &&
-	                grow_pinned(d.h_pin, d.cap_pin, nb + 1 + nch) && grow(d.d_statv, d.cap_statv, nch);
+	const bool ok = grow(d.d_a, d.cap_a, out_bytes + 64) && grow(d.d_b, d.cap_b, body_len + 64) && grow(d.d_off, d.cap_off, nblocks + 1) &&
+	                grow_pinned(d.h_pin, d.cap_pin, nblocks + 1 + np) && grow(d.d_statv, d.cap_statv, np);
 	tm.alloc = now_s() - a0;
 	if (!ok)
 		return SNAPPY_BUFFER_TOO_SMALL;
-	memcpy(d.h_pin, off, (nb + 1) * sizeof(uint64_t));
-	uint32_t *h_stat = reinterpret_cast<uint32_t *>(d.h_pin + nb + 1);
-	int rc = SNAPPY_OK;
+	uint64_t *h_off = d.h_pin;
+	uint32_t *h_stat = reinterpret_cast<uint32_t *>(d.h_pin + nblocks + 1);
+	uint64_t *h_off_dev = nullptr;
+	if (cudaHostGetDevicePointer(&h_off_dev, h_off, 0) != cudaSuccess)
+		return SNAPPY_INVALID_INPUT;
+	// all uploads, queued now; event j: bytes [0, pend[j]) have arrived
+	std::vector<uint64_t> pend(np);
 	cudaEventRecord(d.ev_span[0], d.s_in);
-	cudaMemcpyAsync(d.d_off, d.h_pin, (nb + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d.s_in);
-	for (uint64_t i = 0; i < nch && rc == SNAPPY_OK; i++) {
-		const int b = (int)(i & 1);
-		const uint64_t blo = i * cblocks, bhi = std::min(nb, blo + cblocks);
-		const uint64_t c_lo = off[blo], c_bytes = off[bhi] - c_lo;
-		const uint64_t o_lo = blo * (uint64_t)block_size, o_bytes = std::min(out_bytes, bhi * (uint64_t)block_size) - o_lo;
-		if (i >= 2)
-			cudaStreamWaitEvent(d.s_in, d.ev_k[b], 0);
-		cudaMemcpyAsync(d.d_b + b * c_stride, host_comp + c_lo, c_bytes, cudaMemcpyHostToDevice, d.s_in);
-		cudaEventRecord(d.ev_in[b], d.s_in);
-		if (i + 1 == nch)
-			cudaEventRecord(d.ev_span[1], d.s_in);
-		cudaStreamWaitEvent(d.stream, d.ev_in[b], 0);
-		if (i >= 2)
-			cudaStreamWaitEvent(d.stream, d.ev_out[b], 0);
-		if (i == 0)
-			cudaEventRecord(d.ev_span[2], d.stream);
-		// the offsets are relative to the shard; the chunk's bytes start at c_lo
-		rc = pim_snappy_decompress_device(d.d_b + b * c_stride - c_lo, d.d_off + blo, bhi - blo, block_size, o_bytes, d.d_a + b * out_stride,
-		                                  d.d_statv + i, d.stream);
-		cudaEventRecord(d.ev_k[b], d.stream);
-		if (i + 1 == nch)
-			cudaEventRecord(d.ev_span[3], d.stream);
-		cudaStreamWaitEvent(d.s_out, d.ev_k[b], 0);
-		if (i == 0)
-			cudaEventRecord(d.ev_span[4], d.s_out);
-		cudaMemcpyAsync(host_out + o_lo, d.d_a + b * out_stride, o_bytes, cudaMemcpyDeviceToHost, d.s_out);
-		cudaEventRecord(d.ev_out[b], d.s_out);
+	for (uint64_t j = 0, lo = 0; j < np; j++) {
+		cudaMemcpyAsync(d.d_b + lo, body + lo, pieces[j], cudaMemcpyHostToDevice, d.s_in);
+		cudaEventRecord(pool_event(d, j), d.s_in);
+		lo += pieces[j];
+		pend[j] = lo;
 	}
-	cudaStreamWaitEvent(d.s_out, d.ev_k[(nch - 1) & 1], 0);
-	cudaMemcpyAsync(h_stat, d.d_statv, nch * sizeof(uint32_t), cudaMemcpyDeviceToHost, d.s_out);
+	cudaEventRecord(d.ev_span[1], d.s_in);
+	cudaMemsetAsync(d.d_statv, 0, np * sizeof(uint32_t), d.stream);
+	cudaEventRecord(d.ev_span[2], d.stream);
+
+	int rc = SNAPPY_OK;
+	uint64_t launched = 0; // blocks [0, launched) are on their way
+	bool first_out = true;
+	auto launch = [&](uint64_t bhi, uint64_t piece) { // blocks [launched, bhi) end inside pieces 0..piece
+		if (bhi == launched || rc != SNAPPY_OK)
+			return;
+		const uint64_t blo = launched, nb = bhi - blo;
+		const uint64_t o_lo = blo * (uint64_t)block_size, o_bytes = std::min(out_bytes, bhi * (uint64_t)block_size) - o_lo;
+		cudaStreamWaitEvent(d.stream, pool_event(d, piece), 0);
+		fetch_offsets_kernel<<<(unsigned)std::min<uint64_t>(64, (nb + 256) / 256), 256, 0, d.stream>>>(h_off_dev + blo, d.d_off + blo, nb + 1);
+		rc = pim_snappy_decompress_device(d.d_b, d.d_off + blo, nb, block_size, o_bytes, d.d_a + o_lo, d.d_statv + piece, d.stream);
+		cudaEventRecord(pool_event(d, np + piece), d.stream);
+		cudaStreamWaitEvent(d.s_out, pool_event(d, np + piece), 0);
+		if (first_out)
+			cudaEventRecord(d.ev_span[4], d.s_out);
+		first_out = false;
+		cudaMemcpyAsync(host_out + o_lo, d.d_a + o_lo, o_bytes, cudaMemcpyDeviceToHost, d.s_out);
+		launched = bhi;
+	};
+	uint64_t pos = 0, piece = 0;
+	for (uint64_t i = 0; i < nblocks && rc == SNAPPY_OK; i++) {
+		if (pos + 4 > body_len) {
+			rc = SNAPPY_INVALID_INPUT;
+			break;
+		}
+		h_off[i] = pos;
+		const uint32_t cs = (uint32_t)body[pos] | ((uint32_t)body[pos + 1] << 8) | ((uint32_t)body[pos + 2] << 16) | ((uint32_t)body[pos + 3] << 24);
+		pos += 4 + (uint64_t)cs;
+		if (pos > body_len) {
+			rc = SNAPPY_INVALID_INPUT;
+			break;
+		}
+		if (pos > pend[piece]) { // block i ends in a later piece: everything before it goes now
+			launch(i, piece);
+			while (pos > pend[piece])
+				piece++;
+		}
+	}
+	if (rc == SNAPPY_OK && pos != body_len)
+		rc = SNAPPY_INVALID_INPUT;
+	if (rc == SNAPPY_OK) {
+		h_off[nblocks] = pos;
+		launch(nblocks, np - 1);
+	}
+	cudaEventRecord(d.ev_span[3], d.stream);
+	cudaStreamWaitEvent(d.s_out, pool_event(d, np + np - 1), 0);
+	cudaMemcpyAsync(h_stat, d.d_statv, np * sizeof(uint32_t), cudaMemcpyDeviceToHost, d.s_out);
 	cudaEventRecord(d.ev_span[5], d.s_out);
 	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(d.stream) == cudaSuccess &&
 	                    cudaStreamSynchronize(d.s_out) == cudaSuccess;
@@ -429,8 +508,8 @@ int decompress_shard_streamed(DeviceCtx &d, const uint8_t *host_comp, const uint
 	}
 	if (rc != SNAPPY_OK)
 		return rc;
-	for (uint64_t i = 0; i < nch; i++)
-		if (h_stat[i] != 0)
+	for (uint64_t j = 0; j < np; j++)
+		if (h_stat[j] != 0)
 			return SNAPPY_INVALID_INPUT;
 	cudaEventElapsedTime(&tm.copy_in, d.ev_span[0], d.ev_span[1]);
 	cudaEventElapsedTime(&tm.run, d.ev_span[2], d.ev_span[3]);
@@ -731,10 +810,40 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 		return SNAPPY_INVALID_INPUT;
 	const uint64_t nblocks = pim_snappy_num_blocks(out_len, block_size);
 
-	// serial walk over the 4-byte block headers (snappy_decompress.c:317-340)
-	std::vector<uint64_t> off(nblocks + 1);
 	const uint8_t *body = p;
 	const uint64_t body_len = (uint64_t)(end - body);
+	runtime->pre += now_s() - t0;
+
+	t0 = now_s();
+	int ng = ensure_devices();
+	runtime->load = now_s() - t0;
+	if (ng <= 0) {
+		fprintf(stderr, "pim_snappy: no usable sm_100 GPU; there is no CPU fallback\n");
+		return SNAPPY_INVALID_INPUT;
+	}
+	if ((uint64_t)ng > nblocks)
+		ng = (int)nblocks;
+
+	// One device and a large stream: upload, header walk, kernels and download all overlap.
+	if (ng == 1 && chunk_bytes() && out_len > 2 * chunk_bytes()) {
+		DeviceCtx &d = g_devs[0];
+		cudaSetDevice(d.dev);
+		ShardTimes t1;
+		const int r = decompress_stream_resident(d, body, body_len, nblocks, block_size, out_len, output->buffer, t1);
+		if (r != SNAPPY_OK)
+			return (snappy_status)r;
+		runtime->d_alloc = t1.alloc;
+		runtime->copy_in = t1.copy_in * 1e-3;
+		runtime->run = t1.run * 1e-3;
+		runtime->copy_out = t1.copy_out * 1e-3;
+		input->curr = const_cast<uint8_t *>(end);
+		output->curr = output->buffer + out_len;
+		return SNAPPY_OK;
+	}
+
+	// serial walk over the 4-byte block headers (snappy_decompress.c:317-340)
+	t0 = now_s();
+	std::vector<uint64_t> off(nblocks + 1);
 	uint64_t pos = 0;
 	for (uint64_t i = 0; i < nblocks; i++) {
 		if (pos + 4 > body_len)
@@ -750,16 +859,6 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 		return SNAPPY_INVALID_INPUT;
 	runtime->pre += now_s() - t0;
 
-	t0 = now_s();
-	int ng = ensure_devices();
-	runtime->load = now_s() - t0;
-	if (ng <= 0) {
-		fprintf(stderr, "pim_snappy: no usable sm_100 GPU; there is no CPU fallback\n");
-		return SNAPPY_INVALID_INPUT;
-	}
-	if ((uint64_t)ng > nblocks)
-		ng = (int)nblocks;
-
 	std::vector<ShardTimes> tm(ng);
 	std::vector<int> rc(ng, SNAPPY_OK);
 	for_each_shard(ng, [&](int g) {
@@ -771,13 +870,6 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 		const uint64_t o_lo = lo * (uint64_t)block_size;
 		const uint64_t o_bytes = std::min(out_len, hi * (uint64_t)block_size) - o_lo;
 		cudaSetDevice(d.dev);
-		if (chunk_bytes() && o_bytes > 2 * chunk_bytes()) { // stream the shard chunk by chunk
-			std::vector<uint64_t> rel(nb + 1);
-			for (uint64_t i = 0; i <= nb; i++)
-				rel[i] = off[lo + i] - c_lo;
-			rc[g] = decompress_shard_streamed(d, body + c_lo, rel.data(), nb, block_size, o_bytes, output->buffer + o_lo, tm[g]);
-			return;
-		}
 		const double a0 = now_s();
 		bool ok = grow(d.d_a, d.cap_a, o_bytes + 64) && grow(d.d_b, d.cap_b, c_bytes + 64) && grow(d.d_off, d.cap_off, nb + 1);
 		tm[g].alloc = now_s() - a0;
