@@ -367,7 +367,7 @@ def run_ours(args):
         dt = max_over_ranks(time.perf_counter() - t0) / args.steps
         sync_all()
         csum = sum(clens)
-        e2e = {"value": total_U / dt / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(U + csum), "d2h_bytes_per_step": int(csum + U),
+        e2e = {"value": total_U / dt / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(sum_over_ranks(U + csum)), "d2h_bytes_per_step": int(sum_over_ranks(csum + U)),
                "ms_per_step": dt * 1e3, "distinct_host_streams": distinct,
                "compress_gbps": U * args.steps / phase["compress"] / 1e9, "decompress_gbps": U * args.steps / phase["decompress"] / 1e9,
                "pinned_copy": pcie,
@@ -381,7 +381,7 @@ def run_ours(args):
         line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
                 "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
                 "data": "synthetic",
-                "config": {"workload": workload_name(args, world), "l2": "inputs (8 GiB per GPU) far exceed the 126 MB L2; no flush needed",
+                "config": {"workload": workload_name(args, world), "l2": f"inputs ({U / GIB:g} GiB per GPU, every stream read once per step) far exceed the 126 MB L2; no flush needed",
                            "compressed_fraction": comp_bytes / U, "bytes_per_gpu": U},
                 "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks}

@@ -16,6 +16,9 @@
 // exclusive scan, and a compaction kernel moves every block to its final offset, yielding
 // the contiguous ( u32 size | elements )* stream of the file format.
 
+#include <algorithm>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "compress_warp.cuh"
 
@@ -29,57 +32,111 @@ __host__ __device__ inline uint32_t slot_stride(uint32_t block_size)
 	return (4u + 32u + block_size + block_size / 6u + 15u) & ~15u;
 }
 
+// Persistent CTAs: at most this many (the global-memory hash tables in scratch are sized by it).
+constexpr uint32_t MAX_PERSIST_CTAS = 1024;
+#ifndef PIM_COMPRESS_PAIRS
+#define PIM_COMPRESS_PAIRS 2
+#endif
+static_assert(PIM_COMPRESS_PAIRS >= 1 && PIM_COMPRESS_PAIRS <= 4, "1..4 pairs");
+constexpr uint32_t NPAIRS = PIM_COMPRESS_PAIRS; // (parser, emitter) warp pairs per CTA: pair 0 with its table in shared memory, the others in global memory
+
 __host__ __device__ inline uint32_t compress_smem_bytes(uint32_t block_size)
 {
-	return 2u * table_entries(block_size) + 16u + (uint32_t)sizeof(EmitRing);
+	return 2u * table_entries(block_size) + 16u + NPAIRS * (uint32_t)sizeof(EmitRing) + 16u;
 }
 
 // The parse reads up to TAIL_SLACK bytes past a block's end.  Inside the stream that is the next
 // block; the stream's last block is read from a copy in scratch that has the slack behind it.
 constexpr uint32_t TAIL_SLACK = 32;
 __host__ __device__ inline uint64_t tail_copy_bytes(uint32_t block_size) { return ((uint64_t)block_size + TAIL_SLACK + 16u + 255u) & ~255ull; }
+__host__ __device__ inline uint64_t gtable_bytes(uint32_t block_size) { return (uint64_t)MAX_PERSIST_CTAS * (NPAIRS - 1) * 2u * table_entries(block_size); }
 
-__global__ void __launch_bounds__(64) snappy_compress_kernel(const uint8_t *__restrict__ in, uint64_t in_len, uint32_t block_size,
-                                                             const uint8_t *__restrict__ tail_copy, uint8_t *__restrict__ slots, uint32_t stride,
-                                                             uint32_t *__restrict__ sizes)
+struct CompressArgs {
+	const uint8_t *in;
+	uint64_t in_len;
+	uint32_t block_size, nblocks;
+	const uint8_t *tail_copy;
+	uint8_t *slots;
+	uint32_t stride;
+	uint32_t *sizes;
+	uint32_t *counter;
+};
+
+// One (parser, emitter) warp pair: pulls blocks from the global counter until none are left.
+// GT: the pair's hash table is in global memory (tbytes), else in shared memory.
+// BAR: the pair's named barrier (a compile-time id: with a run-time id ptxas reserves all 16 barriers
+// for the CTA, which costs resident CTAs).
+template <bool GT, int BAR>
+__device__ __forceinline__ void compress_pair(const CompressArgs &a, uint8_t *tbytes, EmitRing *ring, volatile uint32_t *mail)
+{
+	constexpr int bar_id = BAR;
+	const int lane = lane_id();
+	const bool parser = !((threadIdx.x >> 5) & 1); // else emitter
+	const int ptid = threadIdx.x & 63;
+	for (;;) {
+		if (ptid == 0)
+			*mail = atomicAdd(a.counter, 1u);
+		bar_sync(bar_id, 64);
+		const uint32_t blk = *mail;
+		if (blk >= a.nblocks)
+			break;
+		const uint64_t in_off = blk * (uint64_t)a.block_size;
+		const uint32_t n = (uint32_t)min((uint64_t)a.block_size, a.in_len - in_off);
+		const uint8_t *gsrc = blk + 1 == a.nblocks ? a.tail_copy : a.in + in_off;
+		const uint32_t ts = table_entries(n);
+
+		CBlock c;
+		c.mis = (uint32_t)(reinterpret_cast<uintptr_t>(gsrc) & 3u);
+		c.inw = reinterpret_cast<const uint32_t *>(gsrc - c.mis);
+		c.table = reinterpret_cast<uint16_t *>(tbytes);
+		c.shift = 32 - (31 - __clz(ts)); // snappy_compress.c:288
+		c.out = a.slots + blk * (uint64_t)a.stride;
+		c.n = n;
+
+		for (uint32_t i = ptid * 128u; i < n; i += 64u * 128u) // HBM -> L2 for the whole block, ahead of the parse
+			asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc + i));
+		for (uint32_t i = ptid * 16u; i < 2u * ts; i += 1024u) // get_hash_table, snappy_compress.c:139-146
+			*reinterpret_cast<uint4 *>(tbytes + i) = make_uint4(0, 0, 0, 0);
+		if (ptid == 0) {
+			ring->head = 0;
+			ring->tail = 0;
+		}
+		bar_sync(bar_id, 64);
+
+		if (parser) { // the block's serial chain
+			parse_block_warp<GT>(c, ring);
+		} else { // output bytes only
+			const uint32_t o = emit_block_warp(c, ring);
+			if (lane == 0)
+				a.sizes[blk] = o;
+		}
+		bar_sync(bar_id, 64); // table, ring and mail are reused
+	}
+}
+
+// Persistent CTA = two (parser, emitter) warp pairs, each pulling blocks from a global counter.
+// Pair 0 keeps its hash table in shared memory.  Shared memory holds six such tables per SM and the
+// parse is a latency-bound dependent chain that leaves most issue slots idle, so pair 1 runs a
+// second block per CTA with its table in global memory (L2-resident, ld/st.cg): slower per block,
+// but more blocks in flight per SM.
+__global__ void __launch_bounds__(64 * NPAIRS) snappy_compress_kernel(CompressArgs a, uint8_t *__restrict__ gtables, uint32_t pair_mask)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
-	const int lane = lane_id();
-	const int tid = threadIdx.x;
-	const uint64_t blk = blockIdx.x;
-	const uint64_t in_off = blk * (uint64_t)block_size;
-	const uint32_t n = (uint32_t)min((uint64_t)block_size, in_len - in_off);
-	const uint8_t *gsrc = blk + 1 == gridDim.x ? tail_copy : in + in_off;
-
-	const uint32_t ts_max = table_entries(block_size);
-	const uint32_t ts = table_entries(n);
-
-	CBlock c;
-	c.mis = (uint32_t)(reinterpret_cast<uintptr_t>(gsrc) & 3u);
-	c.inw = reinterpret_cast<const uint32_t *>(gsrc - c.mis);
-	c.table = reinterpret_cast<uint16_t *>(sm);
-	c.shift = 32 - (31 - __clz(ts)); // snappy_compress.c:288
-	c.out = slots + blk * (uint64_t)stride;
-	c.n = n;
-
-	EmitRing *ring = reinterpret_cast<EmitRing *>(sm + 2u * ts_max + 16u);
-	for (uint32_t i = tid * 128u; i < n; i += 64u * 128u) // HBM -> L2 for the whole block, ahead of the parse
-		asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc + i));
-	for (uint32_t i = tid * 16u; i < 2u * ts; i += 1024u)
-		*reinterpret_cast<uint4 *>(sm + i) = make_uint4(0, 0, 0, 0);
-	if (tid == 0) {
-		ring->head = 0;
-		ring->tail = 0;
-	}
-	__syncthreads();
-
-	if (tid < 32) { // parser warp: the block's serial chain
-		parse_block_warp(c, ring);
-	} else { // emitter warp: output bytes only
-		const uint32_t o = emit_block_warp(c, ring);
-		if (lane == 0)
-			sizes[blk] = o;
-	}
+	const int pair = threadIdx.x >> 6;
+	if (!((pair_mask >> pair) & 1u))
+		return;
+	const uint32_t ts_max = table_entries(a.block_size);
+	EmitRing *ring = reinterpret_cast<EmitRing *>(sm + 2u * ts_max + 16u) + pair;
+	volatile uint32_t *mail = reinterpret_cast<volatile uint32_t *>(sm + 2u * ts_max + 16u + NPAIRS * sizeof(EmitRing)) + pair;
+	uint8_t *gt = gtables + ((uint64_t)blockIdx.x * (NPAIRS - 1) + (pair - 1)) * 2u * ts_max;
+	if (pair == 0)
+		compress_pair<false, 1>(a, sm, ring, mail);
+	else if (pair == 1)
+		compress_pair<true, 2>(a, gt, ring, mail);
+	else if (pair == 2)
+		compress_pair<true, 3>(a, gt, ring, mail);
+	else
+		compress_pair<true, 4>(a, gt, ring, mail);
 }
 
 // Exclusive scan of the per-block sizes into 64-bit offsets (one CTA; nblocks is at most a few
@@ -155,7 +212,7 @@ extern "C" uint64_t pim_snappy_compress_bound(uint64_t input_len, uint32_t block
 extern "C" uint64_t pim_snappy_compress_scratch_bytes(uint64_t input_len, uint32_t block_size)
 {
 	const uint64_t nb = pim_snappy_num_blocks(input_len, block_size);
-	return ((nb * 4 + 255) & ~255ull) + tail_copy_bytes(block_size) + nb * (uint64_t)slot_stride(block_size) + 256;
+	return ((nb * 4 + 255) & ~255ull) + 256 + tail_copy_bytes(block_size) + gtable_bytes(block_size) + nb * (uint64_t)slot_stride(block_size) + 256;
 }
 
 extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch,
@@ -172,8 +229,11 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 		return SNAPPY_OK;
 	}
 	uint32_t *sizes = reinterpret_cast<uint32_t *>(d_scratch);
-	uint8_t *tail_copy = d_scratch + ((nb * 4 + 255) & ~255ull);
-	uint8_t *slots = tail_copy + tail_copy_bytes(block_size);
+	uint32_t *counter = reinterpret_cast<uint32_t *>(d_scratch + ((nb * 4 + 255) & ~255ull));
+	uint8_t *tail_copy = reinterpret_cast<uint8_t *>(counter) + 256;
+	uint8_t *gtables = tail_copy + tail_copy_bytes(block_size);
+	uint8_t *slots = gtables + gtable_bytes(block_size);
+	PIM_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
 	// the stream's last block, with readable slack behind it (same 4-byte phase as in the stream)
 	const uint64_t last_off = (nb - 1) * (uint64_t)block_size;
 	tail_copy += reinterpret_cast<uintptr_t>(d_in + last_off) & 15u;
@@ -181,17 +241,37 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 	const uint32_t stride = slot_stride(block_size);
 	const uint32_t smem = compress_smem_bytes(block_size);
 
-	static int configured_for[64] = {0};
+	static int max_ctas[64] = {0}; // per device: resident CTAs of the whole GPU at the largest block size
+	static int sm_count[64] = {0};
 	int dev = 0;
 	PIM_CUDA_TRY(cudaGetDevice(&dev));
-	if (dev < 64 && !configured_for[dev]) {
+	if (dev >= 64)
+		return SNAPPY_INVALID_INPUT;
+	if (!max_ctas[dev]) {
 		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
 		                                  (int)compress_smem_bytes(PIM_SNAPPY_MAX_BLOCK_SIZE)));
 		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-		configured_for[dev] = 1;
+		PIM_CUDA_TRY(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+		max_ctas[dev] = 1;
 	}
+	int per_sm = 0;
+	PIM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, snappy_compress_kernel, 64 * NPAIRS, smem));
+	const uint64_t resident = std::min<uint64_t>(MAX_PERSIST_CTAS, (uint64_t)std::max(per_sm, 1) * sm_count[dev]);
+	const char *pm = getenv("PIM_SNAPPY_PAIRS");
+	const uint32_t pair_mask = pm ? (uint32_t)atoi(pm) : (1u << NPAIRS) - 1u;
+	const unsigned grid = (unsigned)std::min<uint64_t>(resident, (nb + (uint32_t)__builtin_popcount(pair_mask) - 1) / (uint32_t)__builtin_popcount(pair_mask));
 	prof_begin(0, st);
-	snappy_compress_kernel<<<(unsigned)nb, 64, smem, st>>>(d_in, input_len, block_size, tail_copy, slots, stride, sizes);
+	CompressArgs ca;
+	ca.in = d_in;
+	ca.in_len = input_len;
+	ca.block_size = block_size;
+	ca.nblocks = (uint32_t)nb;
+	ca.tail_copy = tail_copy;
+	ca.slots = slots;
+	ca.stride = stride;
+	ca.sizes = sizes;
+	ca.counter = counter;
+	snappy_compress_kernel<<<grid, 64 * NPAIRS, smem, st>>>(ca, gtables, pair_mask);
 	prof_end(0, st);
 	prof_begin(1, st);
 	scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, nb, d_block_off);

@@ -62,7 +62,7 @@ inline uint32_t cw_table_entries(uint32_t n) // snappy_compress.c:139-146
 struct CBlock {
 	const uint32_t *inw; // 4-byte aligned; input byte i is byte (i + mis) from here (global memory, L2-resident, on the device)
 	uint32_t mis;        // 0..15; 24 readable bytes follow the input
-	uint16_t *table;     // zeroed, cw_table_entries(n) entries
+	uint16_t *table;     // zeroed, cw_table_entries(n) entries (shared memory, or global memory for parse_block_warp<true>)
 	int shift;           // 32 - log2(entries), snappy_compress.c:288
 	uint8_t *out;        // output slot: 4-byte size field + elements
 	uint32_t n;          // input bytes
@@ -438,6 +438,8 @@ PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring)
 }
 
 // Parser warp: runs the passes of one block and publishes one record per pass.
+// GT: the hash table lives in global memory (L2) instead of shared memory.
+template <bool GT>
 PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 {
 	using namespace cw;
@@ -477,20 +479,20 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 			if (valid) {
 				in_load128(c, p, cur);
 				h = (cur[0] * 0x1e35a7bdu) >> c.shift; // :161-166
-				tc = c.table[h];
+				tc = wp::tbl_ld<GT>(c.table, h);
 			}
 			wp::syncwarp(); // every lane has read its slot before anyone writes
 			// Speculative insert + read-back: a lane that does not read its own position back shares
 			// its slot with another lane of this pass.
 			uint32_t w1 = p;
 			if (valid) {
-				c.table[h] = (uint16_t)p;
+				wp::tbl_st<GT>(c.table, h, p);
 				cand = tc;
 				mlen = common_prefix16(c, tc, cur);
 			}
 			wp::syncwarp();
 			if (valid)
-				w1 = c.table[h];
+				w1 = wp::tbl_ld<GT>(c.table, h);
 			const uint32_t inval = wp::ballot(!valid);
 			const uint32_t dup1 = wp::ballot(w1 != p);
 			uint32_t same = mybit, lowmask = 0;
@@ -498,10 +500,10 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 				CW_STAT(6);
 				uint32_t w2 = p;
 				if (valid && w1 != p)
-					c.table[h] = (uint16_t)p;
+					wp::tbl_st<GT>(c.table, h, p);
 				wp::syncwarp();
 				if (valid)
-					w2 = c.table[h];
+					w2 = wp::tbl_ld<GT>(c.table, h);
 				const bool involved = valid && (w1 != p || w2 != p);
 				same = wp::match_any(involved ? h : 0xFFFFFFFFu);
 				if (!involved)
@@ -548,11 +550,11 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 			// ---- table: undo the speculative inserts of lanes that were not inserted -----------
 			if (w.outcome != 2) {
 				if (valid && !inI)
-					c.table[h] = (uint16_t)tc;
+					wp::tbl_st<GT>(c.table, h, tc);
 				if (dup1) { // shared slots: the last inserted lane of the group owns the slot
 					wp::syncwarp();
 					if (inI && !(same & Imask & ~le))
-						c.table[h] = (uint16_t)p;
+						wp::tbl_st<GT>(c.table, h, p);
 				}
 			}
 

@@ -23,6 +23,8 @@ uint32_t reduce_max(uint32_t v);
 void syncwarp();
 void spin_pause();  // inside a wait loop on shared memory written by another warp
 inline void fence_block() {}
+template <bool GT> inline uint32_t tbl_ld(const uint16_t *t, uint32_t h) { return t[h]; }
+template <bool GT> inline void tbl_st(uint16_t *t, uint32_t h, uint32_t v) { t[h] = (uint16_t)v; }
 inline uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
 {
 	sh &= 31u;
@@ -48,6 +50,23 @@ __device__ __forceinline__ uint32_t reduce_max(uint32_t v) { return __reduce_max
 __device__ __forceinline__ void syncwarp() { __syncwarp(); }
 __device__ __forceinline__ void spin_pause() { __nanosleep(20); }
 __device__ __forceinline__ void fence_block() { __threadfence_block(); }
+// hash-table access: shared memory (GT = false), or global memory served by L2 (GT = true; .cg so that
+// the lanes of the warp always see each other's stores)
+template <bool GT> __device__ __forceinline__ uint32_t tbl_ld(const uint16_t *t, uint32_t h)
+{
+	if (!GT)
+		return t[h];
+	uint16_t v;
+	asm volatile("ld.global.cg.u16 %0, [%1];" : "=h"(v) : "l"(t + h) : "memory");
+	return v;
+}
+template <bool GT> __device__ __forceinline__ void tbl_st(uint16_t *t, uint32_t h, uint32_t v)
+{
+	if (!GT)
+		t[h] = (uint16_t)v;
+	else
+		asm volatile("st.global.cg.u16 [%0], %1;" ::"l"(t + h), "h"((uint16_t)v) : "memory");
+}
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) { return __funnelshift_r(lo, hi, sh); }
 __device__ __forceinline__ int ffs32(uint32_t v) { return __ffs((int)v); }
 __device__ __forceinline__ int clz32(uint32_t v) { return __clz((int)v); }

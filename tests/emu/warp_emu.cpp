@@ -190,7 +190,7 @@ void body(void *arg)
 {
 	Job *j = static_cast<Job *>(arg);
 	if (g_cur < NL) {
-		pimsnappy::parse_block_warp(j->blk, &j->ring);
+		pimsnappy::parse_block_warp<false>(j->blk, &j->ring);
 	} else {
 		const uint32_t r = pimsnappy::emit_block_warp(j->blk, &j->ring);
 		if (pimsnappy::wp::lane() == 0)
