@@ -48,7 +48,10 @@ __device__ __forceinline__ uint32_t shfl(uint32_t v, int src_lane) { return __sh
 __device__ __forceinline__ uint32_t match_any(uint32_t v) { return __match_any_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ uint32_t reduce_max(uint32_t v) { return __reduce_max_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ void syncwarp() { __syncwarp(); }
-__device__ __forceinline__ void spin_pause() { __nanosleep(20); }
+#ifndef PIM_SPIN_NS
+#define PIM_SPIN_NS 20
+#endif
+__device__ __forceinline__ void spin_pause() { __nanosleep(PIM_SPIN_NS); }
 __device__ __forceinline__ void fence_block() { __threadfence_block(); }
 // hash-table access: shared memory (GT = false), or global memory served by L2 (GT = true; .cg so that
 // the lanes of the warp always see each other's stores)
