@@ -102,6 +102,7 @@ struct DeviceCtx {
 	uint64_t *h_small = nullptr;                    // pinned: [0] total, [1] status
 	// chunked pipeline (H2D | kernels | D2H on three streams, two buffers each)
 	cudaStream_t s_in = nullptr, s_out = nullptr, stream2 = nullptr;
+	cudaStream_t cs_more[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // further compute streams of the compress pipeline
 	std::vector<cudaEvent_t> ev_pool;               // per-group events of the streamed paths (untimed)
 	cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
 	cudaEvent_t ev_span[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // first/last of each stream
@@ -135,6 +136,7 @@ int init_devices_locked(const int *ids, int n)
 		if (d.s_in) cudaStreamDestroy(d.s_in);
 		if (d.s_out) cudaStreamDestroy(d.s_out);
 		if (d.stream2) cudaStreamDestroy(d.stream2);
+		for (auto &c : d.cs_more) if (c) cudaStreamDestroy(c);
 		for (auto &e : d.ev_pool) if (e) cudaEventDestroy(e);
 		for (auto &e : d.ev_in) if (e) cudaEventDestroy(e);
 		for (auto &e : d.ev_k) if (e) cudaEventDestroy(e);
@@ -170,6 +172,9 @@ int init_devices_locked(const int *ids, int n)
 		if (cudaStreamCreateWithFlags(&d.s_in, cudaStreamNonBlocking) != cudaSuccess) continue;
 		if (cudaStreamCreateWithFlags(&d.s_out, cudaStreamNonBlocking) != cudaSuccess) continue;
 		if (cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking) != cudaSuccess) continue;
+		bool more_ok = true;
+		for (auto &c : d.cs_more) more_ok = more_ok && cudaStreamCreateWithFlags(&c, cudaStreamNonBlocking) == cudaSuccess;
+		if (!more_ok) continue;
 		for (auto &e : d.ev_in) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
 		for (auto &e : d.ev_k) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
 		for (auto &e : d.ev_out) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
@@ -233,11 +238,22 @@ uint64_t chunk_bytes()
 	uint64_t v = g_chunk_bytes.load(std::memory_order_relaxed);
 	if (v == ~uint64_t(0)) {
 		const char *e = getenv("PIM_SNAPPY_CHUNK_MIB");
-		const long mib = e ? atol(e) : 64;
+		const long mib = e ? atol(e) : 32;
 		v = mib <= 0 ? uint64_t(0) : uint64_t(mib) << 20;
 		g_chunk_bytes.store(v, std::memory_order_relaxed);
 	}
 	return v;
+}
+
+// Compute streams the streamed compress path spreads its groups over ($PIM_SNAPPY_STREAMS, 1..8).
+int compress_streams()
+{
+	static const int ns = [] {
+		const char *e = getenv("PIM_SNAPPY_STREAMS");
+		const int v = e ? atoi(e) : 8;
+		return v < 1 ? 1 : (v > 8 ? 8 : v);
+	}();
+	return ns;
 }
 
 size_t put_varint32(uint8_t *p, uint32_t v) // snappy_compress.c:69-98
@@ -343,6 +359,11 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 	const uint64_t ng = groups.size();
 	const uint64_t gmax = *std::max_element(groups.begin(), groups.end());
 	const uint64_t scratch_stride = align256(pim_snappy_compress_scratch_bytes(gmax * block_size, block_size));
+	// The groups' kernels go round robin over NS compute streams.  A block takes about a millisecond
+	// and the GPU holds ~1800 of them at a time, so a group's kernel is short of blocks at its start
+	// and its end: several groups have to be in flight for the SMs to stay full.
+	const int NS = compress_streams();
+	cudaStream_t cs[8] = {d.stream, d.stream2, d.cs_more[0], d.cs_more[1], d.cs_more[2], d.cs_more[3], d.cs_more[4], d.cs_more[5]};
 	// group g: blocks [blo[g], blo[g+1]), compacted output at d_b + out_at[g], offsets at d_off + off_at[g]
 	std::vector<uint64_t> blo(ng + 1, 0), out_at(ng + 1, 0), off_at(ng + 1, 0);
 	for (uint64_t g = 0; g < ng; g++) {
@@ -351,7 +372,7 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 		off_at[g + 1] = off_at[g] + groups[g] + 1;
 	}
 	const double a0 = now_s();
-	const bool ok = grow(d.d_a, d.cap_a, in_bytes + 64) && grow(d.d_b, d.cap_b, out_at[ng]) && grow(d.d_scratch, d.cap_s, 2 * scratch_stride) &&
+	const bool ok = grow(d.d_a, d.cap_a, in_bytes + 64) && grow(d.d_b, d.cap_b, out_at[ng]) && grow(d.d_scratch, d.cap_s, NS * scratch_stride) &&
 	                grow(d.d_off, d.cap_off, off_at[ng]) && grow_pinned(d.h_pin, d.cap_pin, ng);
 	tm.alloc = now_s() - a0;
 	if (!ok)
@@ -364,8 +385,6 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 		cudaEventRecord(pool_event(d, g), d.s_in);
 	}
 	cudaEventRecord(d.ev_span[1], d.s_in);
-	// the two compute streams alternate, so that the tail of one group's kernel overlaps the next group
-	cudaStream_t cs[2] = {d.stream, d.stream2};
 	int rc = SNAPPY_OK;
 	uint64_t at = 0; // host offset of the next compressed group
 	auto finish = [&](uint64_t g) { // group g's size is known once its kernels are done: queue its D2H
@@ -380,25 +399,29 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 		at += t;
 	};
 	cudaEventRecord(d.ev_span[2], cs[0]);
+	uint64_t finished = 0; // groups whose D2H is queued (in order: the groups land back to back)
 	for (uint64_t g = 0; g < ng && rc == SNAPPY_OK; g++) {
-		cudaStream_t st = cs[g & 1];
+		cudaStream_t st = cs[g % NS];
 		const uint64_t lo = blo[g] * block_size, bytes = std::min(in_bytes, blo[g + 1] * block_size) - lo;
 		cudaStreamWaitEvent(st, pool_event(d, g), 0);
-		rc = pim_snappy_compress_device(d.d_a + lo, bytes, block_size, d.d_scratch + (g & 1) * scratch_stride, scratch_stride, d.d_b + out_at[g],
+		rc = pim_snappy_compress_device(d.d_a + lo, bytes, block_size, d.d_scratch + (g % NS) * scratch_stride, scratch_stride, d.d_b + out_at[g],
 		                                d.d_off + off_at[g], st);
 		cudaMemcpyAsync(d.h_pin + g, d.d_off + off_at[g] + groups[g], sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
 		cudaEventRecord(pool_event(d, ng + g), st);
-		if (g >= 1 && rc == SNAPPY_OK)
-			finish(g - 1);
+		while (rc == SNAPPY_OK && finished + (uint64_t)(NS - 1) <= g) // keep NS - 1 groups queued behind the running one
+			finish(finished++);
 	}
-	if (rc == SNAPPY_OK)
-		finish(ng - 1);
+	while (rc == SNAPPY_OK && finished < ng)
+		finish(finished++);
 	cudaEventRecord(d.ev_span[5], d.s_out);
-	// span 3 closes the kernels' interval: after both compute streams
-	cudaStreamWaitEvent(cs[0], pool_event(d, ng + ng - 1), 0);
+	// span 3 closes the kernels' interval: after every compute stream
+	for (uint64_t g = ng > (uint64_t)NS ? ng - NS : 0; g < ng; g++)
+		cudaStreamWaitEvent(cs[0], pool_event(d, ng + g), 0);
 	cudaEventRecord(d.ev_span[3], cs[0]);
-	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(cs[0]) == cudaSuccess &&
-	                    cudaStreamSynchronize(cs[1]) == cudaSuccess && cudaStreamSynchronize(d.s_out) == cudaSuccess;
+	bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess;
+	for (int k = 0; k < NS; k++)
+		synced = cudaStreamSynchronize(cs[k]) == cudaSuccess && synced;
+	synced = cudaStreamSynchronize(d.s_out) == cudaSuccess && synced;
 	if (!synced) {
 		fprintf(stderr, "pim_snappy: compress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
 		return SNAPPY_INVALID_INPUT;

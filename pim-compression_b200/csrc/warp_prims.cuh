@@ -49,7 +49,7 @@ __device__ __forceinline__ uint32_t match_any(uint32_t v) { return __match_any_s
 __device__ __forceinline__ uint32_t reduce_max(uint32_t v) { return __reduce_max_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ void syncwarp() { __syncwarp(); }
 #ifndef PIM_SPIN_NS
-#define PIM_SPIN_NS 20
+#define PIM_SPIN_NS 400
 #endif
 __device__ __forceinline__ void spin_pause() { __nanosleep(PIM_SPIN_NS); }
 __device__ __forceinline__ void fence_block() { __threadfence_block(); }

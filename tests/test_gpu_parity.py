@@ -228,7 +228,31 @@ def test_streamed_host_path_matches_single_shot(P, oracle):
         with pytest.raises(P.SnappyError):
             P.decompress(bad)
     finally:
-        P.set_chunk_bytes(128 << 20)
+        P.set_chunk_bytes(32 << 20)  # the library's default
+
+
+def test_multi_gpu_shards_match_single_gpu(P, oracle):
+    """with N GPUs the shim splits the blocks into contiguous ranges (snappy_compress.c:495),
+    one host thread per GPU, and stitches on the host -- the bytes must not depend on N."""
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("needs at least two GPUs")
+    data = P.synth_host(P.SYNTH_MIX, 0x2B200, (9 << 20) + 4097)
+    try:
+        for bs in (32768, 4096, 65536):
+            want = oracle.compress(data, bs)
+            for n in sorted({2, ndev}):
+                assert P.set_devices(list(range(n))) == n
+                got = P.compress(data, bs)
+                assert got.size == want.size and np.array_equal(got, want), (bs, n)
+                assert np.array_equal(P.decompress(want), data), (bs, n)
+        # fewer blocks than GPUs
+        tiny = data[:40000]
+        assert np.array_equal(P.compress(tiny, 32768), oracle.compress(tiny, 32768))
+        assert np.array_equal(P.decompress(oracle.compress(tiny, 32768)), tiny)
+    finally:
+        P.set_devices([0])
 
 
 def test_cli_matches_reference_contract(P, golden, tmp_path):
