@@ -31,8 +31,17 @@
 namespace pimsnappy {
 namespace {
 
-constexpr int WARPS = 4;                 // independent warps (= blocks in flight) per CTA
-constexpr uint32_t RING = 4096;          // bytes of recent output kept in shared memory
+#ifndef PIM_DEC_WARPS
+#define PIM_DEC_WARPS 4
+#endif
+#ifndef PIM_DEC_RING
+#define PIM_DEC_RING 4096
+#endif
+#ifndef PIM_DEC_MINB
+#define PIM_DEC_MINB 6
+#endif
+constexpr int WARPS = PIM_DEC_WARPS;     // independent warps (= blocks in flight) per CTA
+constexpr uint32_t RING = PIM_DEC_RING;  // bytes of recent output kept in shared memory
 constexpr uint32_t RMASK = RING - 1;
 constexpr uint32_t SEGB = 32;            // compressed bytes per lane
 constexpr uint32_t CHUNK = 32 * SEGB;    // compressed bytes per parse step
@@ -42,6 +51,10 @@ constexpr uint32_t MAX_REC = CHUNK / 2;  // an element occupies >= 2 compressed 
 constexpr uint32_t SHORT_LIT = 60;       // literals up to this long are served from the staged bytes
 constexpr uint32_t RUNAHEAD = RING / 4;  // the window stops fetching when this far ahead of the frontier
 constexpr uint32_t KEEP = 80;            // bytes of a long literal's end that are also put into the ring
+// One refill fetches up to 32 elements of at most 64 bytes on top of the run-ahead: everything between the
+// write frontier and the last fetched byte must fit the ring (measured on B200: a 2 KB ring with 7 or 8 CTAs
+// per SM is only ~3 % faster on SYN-MIX and breaks this bound, so the ring stays at 4 KB).
+static_assert((RING & (RING - 1)) == 0 && RING >= RUNAHEAD + 32 * 64 + 64, "ring too small for the element window");
 
 // per-warp shared memory (byte offsets from the warp's base)
 constexpr uint32_t WS_RING = 0;                         // RING + 32 (over-read slack)
@@ -574,7 +587,7 @@ __device__ __forceinline__ void decode_block(Dec &d)
 // Kernel: persistent CTAs of WARPS independent warps; warp g of the grid decodes blocks
 // g, g + total_warps, ...
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(32 * WARPS, 6) snappy_decompress_kernel(const uint8_t *__restrict__ comp, const uint64_t *__restrict__ block_off,
+__global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_kernel(const uint8_t *__restrict__ comp, const uint64_t *__restrict__ block_off,
                                                                           uint64_t nblocks, uint32_t block_size, uint64_t out_len,
                                                                           uint8_t *__restrict__ out, uint32_t *__restrict__ status)
 {

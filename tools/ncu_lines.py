@@ -2,7 +2,8 @@
 """Per-CUDA-source-line aggregation of an .ncu-rep (samples, instructions).  Usage: ncu_lines.py rep [topN]"""
 import csv, subprocess, sys, io, collections
 rep = sys.argv[1]; topn = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+import os
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"] + (["-k", "regex:" + os.environ["KERNEL"]] if os.environ.get("KERNEL") else []), capture_output=True, text=True).stdout
 agg = collections.OrderedDict()
 fname = ""; hdr = None
 for r in csv.reader(io.StringIO(out)):
