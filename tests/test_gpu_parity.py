@@ -273,3 +273,20 @@ def test_cli_matches_reference_contract(P, golden, tmp_path):
     assert f"Decompressed {txt.size} bytes to: {back}" in r.stdout
     assert subprocess.run([cli], capture_output=True).returncode == 255      # missing -i  -> -1
     assert subprocess.run([cli, "-x"], capture_output=True).returncode == 254  # bad option -> -2
+
+
+def test_sweep_tool_writes_reference_csv_layout(P, golden, tmp_path):
+    # the reference's sweep driver, on GPUs; CSV columns as run_tests.py:134 writes them
+    import csv
+    import sys
+    txt, _ = golden["terror2"]
+    src = tmp_path / "terror2.txt"
+    src.write_bytes(txt.tobytes())
+    tool = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "run_tests.py")
+    r = subprocess.run([sys.executable, tool, "-f", str(src), "-g", "1", "-b", "32768", "4096", "-o", str(tmp_path / "results"), "--reps", "1"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rows = list(csv.reader(open(tmp_path / "results" / "terror2_compression_breakdown.csv")))
+    assert rows[0] == ["prepare", "alloc", "load", "copy_in", "run", "copy_out", "free", "dpus"] and rows[1][-1] == "1"
+    blk = list(csv.reader(open(tmp_path / "results" / "compression_vs_blksize.csv")))
+    assert [b[1] for b in blk[1:]] == ["32768", "4096"] and int(blk[1][2]) == golden["terror2"][1].size
