@@ -6,12 +6,18 @@
 // multiplicative hash (:161-166), same per-block table sizing (:139-146), same skip heuristic
 // (:333-348), same order of table updates (:391-397), same element encodings (:202-272).
 //
-// One CTA (two warps) per input block.  The 16-bit hash table lives in shared memory (32 KB for
-// blocks of 16 KB and more: six blocks per SM); the input is NOT staged -- it is prefetched into L2
-// and read from there (sequential window via L1), which doubles the blocks in flight compared to
-// keeping table + input in shared memory.  The parser warp (compress_warp.cuh) fuses the
-// reference's step 1 / step 3 probes into 32-lane passes that resolve several (literal, copy)
-// pairs per shared-memory round trip, the emitter warp turns its per-pass records into bytes.
+// ONE persistent CTA per SM made of (parser, emitter) warp PAIRS; every pair compresses one input
+// block at a time and pulls the next from a global counter.  A block's parse is a serial dependency
+// chain that leaves the SM mostly idle, so throughput is the number of blocks in flight per SM, and
+// that is bounded by where the 16-bit hash tables live (32 KB for blocks of 16 KB and more):
+//   * as many pairs as shared memory holds tables for (seven at 32 KB -- one CTA owning all of the
+//     SM's shared memory fits one more table than six independent CTAs did) keep theirs there;
+//   * as many pairs again keep their table in global memory (L2-resident, ld/st.cg): 0.6x the speed of
+//     a shared-memory pair, and more than one of them per shared-memory pair saturates L2.
+// The input is NOT staged: it is prefetched into L2 and read from there through L1.  The parser warp
+// (compress_warp.cuh) fuses the reference's step 1 / step 3 probes into 32-lane passes that resolve
+// several (literal, copy) pairs per shared-memory round trip, the emitter warp turns its per-pass
+// records into bytes.
 // Each block writes to a fixed worst-case slot; block sizes then go through a device
 // exclusive scan, and a compaction kernel moves every block to its final offset, yielding
 // the contiguous ( u32 size | elements )* stream of the file format.
@@ -32,24 +38,38 @@ __host__ __device__ inline uint32_t slot_stride(uint32_t block_size)
 	return (4u + 32u + block_size + block_size / 6u + 15u) & ~15u;
 }
 
-// Persistent CTAs: at most this many (the global-memory hash tables in scratch are sized by it).
-constexpr uint32_t MAX_PERSIST_CTAS = 1024;
-#ifndef PIM_COMPRESS_PAIRS
-#define PIM_COMPRESS_PAIRS 2
-#endif
-static_assert(PIM_COMPRESS_PAIRS >= 1 && PIM_COMPRESS_PAIRS <= 4, "1..4 pairs");
-constexpr uint32_t NPAIRS = PIM_COMPRESS_PAIRS; // (parser, emitter) warp pairs per CTA: pair 0 with its table in shared memory, the others in global memory
+// Persistent CTAs (one per SM): at most this many, each with at most MAX_GT pairs whose table is in
+// global memory (the tables in scratch are sized by these two).
+constexpr uint32_t MAX_PERSIST_CTAS = 160;
+constexpr uint32_t MAX_GT = 8;
+constexpr uint32_t MAX_PAIRS = 15;   // named barriers 1..15, one per pair
+constexpr uint32_t PAIR_CTL_BYTES = (uint32_t)sizeof(EmitRing) + 4u; // record ring + mail word
 
-__host__ __device__ inline uint32_t compress_smem_bytes(uint32_t block_size)
+// Pairs of one CTA for this block size: n_sm with the table in shared memory, n_gt in global memory.
+inline void plan_pairs(uint32_t block_size, uint32_t smem_budget, uint32_t *n_sm, uint32_t *n_gt)
 {
-	return 2u * table_entries(block_size) + 16u + NPAIRS * (uint32_t)sizeof(EmitRing) + 16u;
+	const uint32_t tbytes = 2u * table_entries(block_size);
+	uint32_t ns = (smem_budget - 64u) / (tbytes + PAIR_CTL_BYTES);
+	ns = std::max(1u, std::min(ns, MAX_PAIRS));
+	const uint32_t ctl_room = (smem_budget - 64u - ns * tbytes) / PAIR_CTL_BYTES; // pairs the rest has control blocks for
+	uint32_t ng = std::min(std::min(MAX_PAIRS - ns, MAX_GT), std::min(ns + 1u, ctl_room > ns ? ctl_room - ns : 0u));
+	if (const char *e = getenv("PIM_SNAPPY_NSM")) // development aids
+		ns = std::max(1u, std::min(ns, (uint32_t)atoi(e)));
+	if (const char *e = getenv("PIM_SNAPPY_NGT"))
+		ng = std::min(ng, (uint32_t)atoi(e));
+	*n_sm = ns;
+	*n_gt = ng;
 }
 
 // The parse reads up to TAIL_SLACK bytes past a block's end.  Inside the stream that is the next
 // block; the stream's last block is read from a copy in scratch that has the slack behind it.
 constexpr uint32_t TAIL_SLACK = 32;
 __host__ __device__ inline uint64_t tail_copy_bytes(uint32_t block_size) { return ((uint64_t)block_size + TAIL_SLACK + 16u + 255u) & ~255ull; }
-__host__ __device__ inline uint64_t gtable_bytes(uint32_t block_size) { return (uint64_t)MAX_PERSIST_CTAS * (NPAIRS - 1) * 2u * table_entries(block_size); }
+__host__ __device__ inline uint64_t gtable_bytes(uint32_t block_size) { return (uint64_t)MAX_PERSIST_CTAS * MAX_GT * 2u * table_entries(block_size); }
+
+#ifndef PIM_PAIR_INLINE
+#define PIM_PAIR_INLINE __forceinline__
+#endif
 
 struct CompressArgs {
 	const uint8_t *in;
@@ -64,15 +84,13 @@ struct CompressArgs {
 
 // One (parser, emitter) warp pair: pulls blocks from the global counter until none are left.
 // GT: the pair's hash table is in global memory (tbytes), else in shared memory.
-// BAR: the pair's named barrier (a compile-time id: with a run-time id ptxas reserves all 16 barriers
-// for the CTA, which costs resident CTAs).
-template <bool GT, int BAR>
-__device__ __forceinline__ void compress_pair(const CompressArgs &a, uint8_t *tbytes, EmitRing *ring, volatile uint32_t *mail)
+// bar_id: the pair's named barrier (run-time ids make ptxas reserve all 16 barriers: fine for one CTA per SM).
+template <bool GT>
+__device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tbytes, EmitRing *ring, volatile uint32_t *mail, int bar_id, uint32_t role)
 {
-	constexpr int bar_id = BAR;
 	const int lane = lane_id();
-	const bool parser = !((threadIdx.x >> 5) & 1); // else emitter
-	const int ptid = threadIdx.x & 63;
+	const bool parser = role == 0; // else emitter
+	const int ptid = (int)role * 32 + lane;
 	for (;;) {
 		if (ptid == 0)
 			*mail = atomicAdd(a.counter, 1u);
@@ -114,29 +132,31 @@ __device__ __forceinline__ void compress_pair(const CompressArgs &a, uint8_t *tb
 	}
 }
 
-// Persistent CTA = two (parser, emitter) warp pairs, each pulling blocks from a global counter.
-// Pair 0 keeps its hash table in shared memory.  Shared memory holds six such tables per SM and the
-// parse is a latency-bound dependent chain that leaves most issue slots idle, so pair 1 runs a
-// second block per CTA with its table in global memory (L2-resident, ld/st.cg): slower per block,
-// but more blocks in flight per SM.
-__global__ void __launch_bounds__(64 * NPAIRS) snappy_compress_kernel(CompressArgs a, uint8_t *__restrict__ gtables, uint32_t pair_mask)
+// The persistent CTA: pairs [0, n_sm) keep their table in shared memory, pairs [n_sm, n_sm + n_gt) in gtables.
+__global__ void __launch_bounds__(64 * MAX_PAIRS, 1) snappy_compress_kernel(CompressArgs a, uint8_t *__restrict__ gtables, uint32_t n_sm, uint32_t n_gt)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
-	const int pair = threadIdx.x >> 6;
-	if (!((pair_mask >> pair) & 1u))
-		return;
-	const uint32_t ts_max = table_entries(a.block_size);
-	EmitRing *ring = reinterpret_cast<EmitRing *>(sm + 2u * ts_max + 16u) + pair;
-	volatile uint32_t *mail = reinterpret_cast<volatile uint32_t *>(sm + 2u * ts_max + 16u + NPAIRS * sizeof(EmitRing)) + pair;
-	uint8_t *gt = gtables + ((uint64_t)blockIdx.x * (NPAIRS - 1) + (pair - 1)) * 2u * ts_max;
-	if (pair == 0)
-		compress_pair<false, 1>(a, sm, ring, mail);
-	else if (pair == 1)
-		compress_pair<true, 2>(a, gt, ring, mail);
-	else if (pair == 2)
-		compress_pair<true, 3>(a, gt, ring, mail);
+	// Warp w runs on scheduler w % 4.  The parsers are the busy warps (an emitter mostly waits), so the
+	// roles are laid out in groups of four warps = two pairs: (parser, parser, emitter, emitter) in even
+	// groups and (emitter, emitter, parser, parser) in odd ones -- every scheduler gets its share of parsers.
+	const uint32_t w = threadIdx.x >> 5, g = w >> 2, k = w & 3, npairs = n_sm + n_gt;
+	uint32_t pair, role; // role 0: parser, 1: emitter
+	if (2 * g + 1 < npairs) {
+		const uint32_t kk = (g & 1) ? (k ^ 2u) : k;
+		pair = 2 * g + (kk & 1u);
+		role = kk >> 1;
+	} else { // a last group of one pair
+		pair = 2 * g;
+		role = k & 1u;
+	}
+	const uint32_t tbytes = 2u * table_entries(a.block_size);
+	uint8_t *ctl = sm + n_sm * tbytes;
+	EmitRing *ring = reinterpret_cast<EmitRing *>(ctl) + pair;
+	volatile uint32_t *mail = reinterpret_cast<volatile uint32_t *>(ctl + npairs * sizeof(EmitRing)) + pair;
+	if (pair < n_sm)
+		compress_pair<false>(a, sm + pair * tbytes, ring, mail, (int)pair + 1, role);
 	else
-		compress_pair<true, 4>(a, gt, ring, mail);
+		compress_pair<true>(a, gtables + ((uint64_t)blockIdx.x * n_gt + (pair - n_sm)) * tbytes, ring, mail, (int)pair + 1, role);
 }
 
 // Exclusive scan of the per-block sizes into 64-bit offsets (one CTA; nblocks is at most a few
@@ -239,27 +259,26 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 	tail_copy += reinterpret_cast<uintptr_t>(d_in + last_off) & 15u;
 	PIM_CUDA_TRY(cudaMemcpyAsync(tail_copy, d_in + last_off, input_len - last_off, cudaMemcpyDeviceToDevice, st));
 	const uint32_t stride = slot_stride(block_size);
-	const uint32_t smem = compress_smem_bytes(block_size);
 
-	static int max_ctas[64] = {0}; // per device: resident CTAs of the whole GPU at the largest block size
+	static int smem_optin[64] = {0}; // per device: opt-in shared memory per CTA
 	static int sm_count[64] = {0};
 	int dev = 0;
 	PIM_CUDA_TRY(cudaGetDevice(&dev));
 	if (dev >= 64)
 		return SNAPPY_INVALID_INPUT;
-	if (!max_ctas[dev]) {
-		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                                  (int)compress_smem_bytes(PIM_SNAPPY_MAX_BLOCK_SIZE)));
+	if (!smem_optin[dev]) {
+		int optin = 0;
+		PIM_CUDA_TRY(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
 		PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_compress_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
 		PIM_CUDA_TRY(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
-		max_ctas[dev] = 1;
+		smem_optin[dev] = optin;
 	}
-	int per_sm = 0;
-	PIM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, snappy_compress_kernel, 64 * NPAIRS, smem));
-	const uint64_t resident = std::min<uint64_t>(MAX_PERSIST_CTAS, (uint64_t)std::max(per_sm, 1) * sm_count[dev]);
-	const char *pm = getenv("PIM_SNAPPY_PAIRS");
-	const uint32_t pair_mask = pm ? (uint32_t)atoi(pm) : (1u << NPAIRS) - 1u;
-	const unsigned grid = (unsigned)std::min<uint64_t>(resident, (nb + (uint32_t)__builtin_popcount(pair_mask) - 1) / (uint32_t)__builtin_popcount(pair_mask));
+	uint32_t n_sm = 0, n_gt = 0;
+	plan_pairs(block_size, (uint32_t)smem_optin[dev], &n_sm, &n_gt);
+	const uint32_t npairs = n_sm + n_gt;
+	const uint32_t smem = n_sm * 2u * table_entries(block_size) + npairs * PAIR_CTL_BYTES + 16u;
+	const unsigned grid = (unsigned)std::min<uint64_t>(std::min<uint64_t>(MAX_PERSIST_CTAS, (uint64_t)sm_count[dev]), (nb + npairs - 1) / npairs);
 	prof_begin(0, st);
 	CompressArgs ca;
 	ca.in = d_in;
@@ -271,7 +290,7 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 	ca.stride = stride;
 	ca.sizes = sizes;
 	ca.counter = counter;
-	snappy_compress_kernel<<<grid, 64 * NPAIRS, smem, st>>>(ca, gtables, pair_mask);
+	snappy_compress_kernel<<<grid, 64 * npairs, smem, st>>>(ca, gtables, n_sm, n_gt);
 	prof_end(0, st);
 	prof_begin(1, st);
 	scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, nb, d_block_off);

@@ -329,7 +329,10 @@ PW_FN void walk_serial(const CBlock &c, Walk &w, bool has_ic, bool valid, uint32
 // block's serial dependency chain.  Everything that only produces output bytes is handed to the
 // EMITTER warp through a small ring of per-pass records in shared memory, so it leaves the chain.
 // ---------------------------------------------------------------------------------------------
-constexpr uint32_t CW_RING = 4; // records in flight between the two warps
+#ifndef PIM_CW_RING
+#define PIM_CW_RING 1
+#endif
+constexpr uint32_t CW_RING = PIM_CW_RING; // records in flight between the two warps
 
 struct EmitRec {
 	uint32_t lanew[32]; // per lane: first byte at its position | match length << 8 | copy offset << 16
@@ -340,7 +343,7 @@ struct EmitRec {
 	uint32_t lit_from, lit_len;   // literal emitted before the window's elements (len 0: none)
 	uint32_t copy_off, copy_len;  // copy emitted after them (len 0: none)
 	uint32_t done;      // last record of the block
-	uint32_t pad[7];
+	uint32_t pad[7];    // (192-byte records: measurably faster than packed ones)
 };
 
 struct EmitRing {

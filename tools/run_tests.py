@@ -89,6 +89,8 @@ def main():
     ap.add_argument("--reps", type=int, default=3, help="runs per point; the fastest total is kept")
     a = ap.parse_args()
     res = pathlib.Path(a.results)
+    for mode in ("compression", "decompression"):  # the reference's scripts expect these to exist, too
+        (res / mode).mkdir(parents=True, exist_ok=True)
     speed = {"compression": [["host", "1", "0"]], "decompression": [["host", "1", "0"]]}
     blk_rows = []
     for f in a.files:
