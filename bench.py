@@ -357,6 +357,16 @@ def run_ours(args):
             c1.record()
             torch.cuda.synchronize()
             pcie[name + "_gbps"] = n / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        # ... and the same with every rank copying both ways at once (what the host side gives N GPUs together)
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        sync_all()
+        tb0 = time.perf_counter()
+        assert rtlib.cudaMemcpyAsync(d_tmp.data_ptr(), h_in[0].ptr, n, 4, s_up.cuda_stream) == 0
+        assert rtlib.cudaMemcpyAsync(h_back.ptr, d_in[0].data_ptr(), n, 4, s_dn.cuda_stream) == 0
+        torch.cuda.synchronize()
+        both = n / (time.perf_counter() - tb0) / 1e9
+        pcie["both_directions_all_ranks_gbps_per_direction"] = {"slowest_rank": -max_over_ranks(-both), "sum_over_ranks": sum_over_ranks(both)}
+        assert np.array_equal(h_back.array[:n], h_in[0].array)  # (h_back now holds stream 0 again)
         sync_all()
         phase["compress"] = phase["decompress"] = 0.0
         t0 = time.perf_counter()
