@@ -19,6 +19,13 @@ void note_launch(unsigned n = 1);
 void prof_begin(int which, cudaStream_t st);
 void prof_end(int which, cudaStream_t st);
 
+// ---- compression with a placement hint (compress_sm100.cu) -----------------
+// alone_on_gpu: no other compress kernel runs next to this one (one-piece calls): a stream with fewer blocks
+// than the GPU has pair slots is spread over all SMs, fewer pairs per SM (each block then runs faster).
+// The streamed host path passes false: several group kernels share the SMs there.
+snappy_status compress_device_placed(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch, uint64_t scratch_bytes,
+                                     uint8_t *d_out, uint64_t *d_block_off, cudaStream_t st, bool alone_on_gpu);
+
 // ---- shared-memory byte-addressed access -----------------------------------
 // All kernels address their dynamic shared memory as one byte array `sm` and
 // keep positions as byte offsets into it.

@@ -238,7 +238,12 @@ extern "C" uint64_t pim_snappy_compress_scratch_bytes(uint64_t input_len, uint32
 extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch,
                                                     uint64_t scratch_bytes, uint8_t *d_out, uint64_t *d_block_off, void *stream)
 {
-	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	return compress_device_placed(d_in, input_len, block_size, d_scratch, scratch_bytes, d_out, d_block_off, static_cast<cudaStream_t>(stream), true);
+}
+
+snappy_status pimsnappy::compress_device_placed(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch,
+                                                uint64_t scratch_bytes, uint8_t *d_out, uint64_t *d_block_off, cudaStream_t st, bool alone_on_gpu)
+{
 	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE)
 		return SNAPPY_BUFFER_TOO_SMALL;
 	const uint64_t nb = pim_snappy_num_blocks(input_len, block_size);
@@ -276,9 +281,16 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 	}
 	uint32_t n_sm = 0, n_gt = 0;
 	plan_pairs(block_size, (uint32_t)smem_optin[dev], &n_sm, &n_gt);
+	const uint64_t ctas_max = std::min<uint64_t>(MAX_PERSIST_CTAS, (uint64_t)sm_count[dev]);
+	static const bool no_spread = getenv("PIM_SNAPPY_NO_SPREAD") != nullptr; // development aid
+	if (alone_on_gpu && !no_spread && nb < ctas_max * (n_sm + n_gt)) { // fewer blocks than pair slots: all SMs, fewer pairs each, shared-memory pairs first
+		const uint32_t need = (uint32_t)((nb + ctas_max - 1) / ctas_max);
+		n_gt = need > n_sm ? std::min(n_gt, need - n_sm) : 0u;
+		n_sm = std::min(n_sm, need);
+	}
 	const uint32_t npairs = n_sm + n_gt;
 	const uint32_t smem = n_sm * 2u * table_entries(block_size) + npairs * PAIR_CTL_BYTES + 16u;
-	const unsigned grid = (unsigned)std::min<uint64_t>(std::min<uint64_t>(MAX_PERSIST_CTAS, (uint64_t)sm_count[dev]), (nb + npairs - 1) / npairs);
+	const unsigned grid = (unsigned)std::min<uint64_t>(ctas_max, (nb + npairs - 1) / npairs);
 	prof_begin(0, st);
 	CompressArgs ca;
 	ca.in = d_in;

@@ -404,8 +404,8 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 		cudaStream_t st = cs[g % NS];
 		const uint64_t lo = blo[g] * block_size, bytes = std::min(in_bytes, blo[g + 1] * block_size) - lo;
 		cudaStreamWaitEvent(st, pool_event(d, g), 0);
-		rc = pim_snappy_compress_device(d.d_a + lo, bytes, block_size, d.d_scratch + (g % NS) * scratch_stride, scratch_stride, d.d_b + out_at[g],
-		                                d.d_off + off_at[g], st);
+		rc = compress_device_placed(d.d_a + lo, bytes, block_size, d.d_scratch + (g % NS) * scratch_stride, scratch_stride, d.d_b + out_at[g],
+		                            d.d_off + off_at[g], st, false);
 		cudaMemcpyAsync(d.h_pin + g, d.d_off + off_at[g] + groups[g], sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
 		cudaEventRecord(pool_event(d, ng + g), st);
 		while (rc == SNAPPY_OK && finished + (uint64_t)(NS - 1) <= g) // keep NS - 1 groups queued behind the running one
