@@ -127,6 +127,7 @@ struct Dec {
 	// write-back state
 	uint32_t fw;          // 16-byte words (of gdst - g15) flushed so far
 	uint32_t ring_lo;     // output bytes below this are not in the ring (they went to HBM directly)
+	bool runs;            // (warp-uniform) some pending element continues a run of copies
 };
 
 __device__ __forceinline__ uint32_t ring_off(const Dec &d, uint32_t p) { return (p + d.g15) & RMASK; }
@@ -262,7 +263,9 @@ struct Window { // one in-flight element per lane
 	uint32_t len;
 	uint32_t off; // K_COPY: distance
 	uint32_t src; // K_LIT / K_LONG
+	uint32_t base; // K_COPY continuing a run of copies with the same distance: output position where the run started, else NO_RUN
 };
+constexpr uint32_t NO_RUN = 0xFFFFFFFFu;
 
 // sixteen bytes at an arbitrary shared-memory byte offset (reads 20 bytes from off & ~3)
 __device__ __forceinline__ void lds128_unaligned(const uint8_t *sm, uint32_t off, uint32_t v[4])
@@ -314,6 +317,21 @@ __device__ __forceinline__ void slow_copy(const Dec &d, const Window &w, uint32_
 			b = p >= ring_floor ? ring[ring_off(d, p)] : ldcg8(d.gdst + p);
 		}
 		ring[ring_off(d, w.dst + k)] = (uint8_t)b;
+	}
+}
+
+// A copy that continues a run of back-to-back copies with the same distance o (zero pages, repeated records:
+// every such element would otherwise wait for the one before it).  From the run's start on the output is
+// periodic with period o, so the element is read from the o bytes before the run's start, whatever its own
+// position: out[dst + k] = out[base - o + ((dst - base + k) mod o)].  Needs only the output below `base`.
+__device__ __forceinline__ void run_copy(const Dec &d, const Window &w)
+{
+	uint8_t *ring = d.ws + WS_RING;
+	const uint32_t pat = w.base - w.off;
+	uint32_t idx = (w.dst - w.base) % w.off;
+	for (uint32_t k = 0; k < w.len; k++) {
+		ring[ring_off(d, w.dst + k)] = ring[ring_off(d, pat + idx)];
+		idx = idx + 1 == w.off ? 0u : idx + 1;
 	}
 }
 
@@ -430,6 +448,15 @@ __device__ __forceinline__ void window_round(Dec &d, Window &w, uint32_t fetched
 	const bool is_copy = w.kind == K_COPY;
 	const uint32_t src_a = w.dst - w.off;
 	const uint32_t src_e = is_copy ? min(src_a + w.len, w.dst) : 0u;
+	// a run member is served from the pattern before its run as soon as that is complete and in the ring
+	if (d.runs) {
+		const bool by_run = w.pend && is_copy && w.base != NO_RUN && w.base <= F && w.base - w.off >= ring_floor && !(src_e <= F);
+		if (by_run) {
+			run_copy(d, w);
+			w.pend = false;
+		}
+		d.runs = __any_sync(FULL, w.pend && w.base != NO_RUN);
+	}
 	const bool ready = w.pend && src_e <= F;
 	// which path
 	const uint32_t dro = ring_off(d, w.dst);
@@ -479,12 +506,14 @@ __device__ __forceinline__ void decode_block(Dec &d)
 	w.pend = false;
 	w.kind = K_LIT;
 	w.dst = w.len = w.off = w.src = 0;
+	w.base = NO_RUN;
 	uint32_t fetched_end = 0; // output position just past the last fetched element
 	uint32_t chunk_base = 0;  // output bytes of the chunks before this one
 	uint32_t cp = 0;
 	int buf = 0;
 	d.fw = 0;
 	d.ring_lo = 0;
+	d.runs = false;
 
 	auto stage_chunk = [&](int b, uint32_t cs) {
 		const uint32_t nstage = cs < d.csize ? min(CHUNK + TAIL, d.csize - cs) : 0u;
@@ -536,6 +565,24 @@ __device__ __forceinline__ void decode_block(Dec &d)
 						w.len = 0;
 					}
 					w.pend = ok && w.kind != K_LONG;
+				}
+				// runs: records of one refill are consecutive elements in lane order, so an element continues a run
+				// iff the closest lower fetching lane holds a copy with the same distance
+				if (took)
+					w.base = NO_RUN;
+				if (__any_sync(FULL, took && w.pend && w.kind == K_COPY && w.off < w.len)) { // (only runs of self-overlapping copies are looked for)
+					const uint32_t tookm = __ballot_sync(FULL, took);
+					const bool cp = took && w.pend && w.kind == K_COPY;
+					const uint32_t lowt = tookm & lt_mask;
+					const int prev = lowt ? 31 - __clz(lowt) : lane;
+					const uint32_t key = cp ? w.off : 0u; // 0 is never a valid distance
+					const uint32_t pkey = __shfl_sync(FULL, key, prev);
+					const bool chained = cp && lowt != 0u && pkey == key;
+					const uint32_t heads = __ballot_sync(FULL, took && !chained) & (lt_mask | (1u << lane));
+					const uint32_t hdst = __shfl_sync(FULL, w.dst, heads ? 31 - __clz(heads) : lane);
+					if (took)
+						w.base = chained ? hdst : NO_RUN;
+					d.runs = d.runs || __any_sync(FULL, chained);
 				}
 				next = min(n, next + (uint32_t)__popc(freem));
 				fetched_end = max(fetched_end, __reduce_max_sync(FULL, took ? w.dst + w.len : 0u));

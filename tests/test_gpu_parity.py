@@ -290,3 +290,19 @@ def test_sweep_tool_writes_reference_csv_layout(P, golden, tmp_path):
     assert rows[0] == ["prepare", "alloc", "load", "copy_in", "run", "copy_out", "free", "dpus"] and rows[1][-1] == "1"
     blk = list(csv.reader(open(tmp_path / "results" / "compression_vs_blksize.csv")))
     assert [b[1] for b in blk[1:]] == ["32768", "4096"] and int(blk[1][2]) == golden["terror2"][1].size
+
+
+def test_periodic_runs(P, oracle):
+    """Runs of back-to-back copies with one distance (zero pages, repeated records) are decoded from the pattern
+    before the run instead of element by element: every period around the element and ring sizes, runs that cross
+    refills, blocks and the 4 KB ring, interleaved with literals."""
+    rng = np.random.default_rng(0xBEEF)
+    parts = []
+    for period in (1, 2, 3, 4, 5, 7, 15, 16, 17, 31, 32, 33, 37, 59, 60, 61, 63, 64, 65, 66, 100, 127, 128, 129, 1000, 2047, 2048, 2049, 4095, 4097, 9000):
+        pat = rng.integers(0, 256, period, dtype=np.uint8)
+        for reps_bytes in (period + 3, 200, 4000, 70000):
+            parts.append(np.tile(pat, reps_bytes // period + 2)[:max(reps_bytes, period + 1)])
+            parts.append(rng.integers(0, 256, int(rng.integers(1, 90)), dtype=np.uint8))
+    data = np.concatenate(parts)
+    for bs in (32768, 65536, 4096, 1000):
+        _roundtrip_check(P, oracle, f"periodic/{bs}", data, bs, ref_decoder_ok=bs < 65536)
