@@ -117,7 +117,8 @@ void pim_snappy_shard_range(uint64_t nblocks, int n_shards, int shard, uint64_t 
 /* The host entry points stream shards larger than two chunks: chunk i+1 is
  * copied to the device while chunk i is coded and chunk i-1 is copied back
  * (what the reference's separate copy_in / run / copy_out phases,
- * snappy_compress.c:560-670, become when they overlap).  Default 64 MiB, or
+ * snappy_compress.c:560-670, become when they overlap; compress groups go round
+ * robin over $PIM_SNAPPY_STREAMS (default 8) compute streams).  Default 32 MiB, or
  * $PIM_SNAPPY_CHUNK_MIB; 0 processes every shard in one piece. */
 void pim_snappy_set_chunk_bytes(uint64_t bytes);
 
@@ -156,6 +157,18 @@ snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_t input_len
 snappy_status pim_snappy_decompress_device(const uint8_t *d_comp, const uint64_t *d_block_off,
                                            uint64_t nblocks, uint32_t block_size, uint64_t out_len,
                                            uint8_t *d_out, uint32_t *d_status, void *stream);
+
+/* One contiguous block stream on ONE GPU from shards that were compressed on several GPUs
+ * (the device-side form of the host stitch, snappy_compress.c:697-703).
+ * Shard g, in block order, lives on device devices[g]: d_shard[g] = its block stream of bytes[g]
+ * bytes, d_shard_off[g] = its u64 offsets [nblocks[g] + 1] relative to the shard (both as written by
+ * pim_snappy_compress_device).  The shards are copied peer to peer (NVLink / NVSwitch where available)
+ * to d_dst on dst_device, back to back, and d_dst_off[0 .. sum(nblocks)] receives the offsets rebased
+ * to d_dst.  Asynchronous on `stream`, a stream of dst_device; the caller orders it after the shards'
+ * producers (events) and passes the shard sizes it read back.  No collective library is involved. */
+snappy_status pim_snappy_gather_shards(int n_shards, const int *devices, const uint8_t *const *d_shard, const uint64_t *bytes,
+                                       const uint64_t *const *d_shard_off, const uint64_t *nblocks, int dst_device,
+                                       uint8_t *d_dst, uint64_t *d_dst_off, void *stream);
 
 /* Optional per-kernel timing.  When enabled, the two device entry points bracket their
  * kernels with CUDA events on the caller's stream; pim_snappy_profile_read() synchronises

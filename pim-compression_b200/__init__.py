@@ -26,6 +26,7 @@ from .api import (  # noqa: F401
     decompress,
     compress_device,
     decompress_device,
+    gather_shards,
     block_offsets,
     synth_host,
     synth_device,

@@ -620,6 +620,54 @@ extern "C" void pim_snappy_shard_range(uint64_t nblocks, int n_shards, int shard
 	}
 	shard_range(nblocks, n_shards, shard, block_lo, block_hi);
 }
+namespace pimsnappy {
+namespace {
+__global__ void rebase_offsets_kernel(uint64_t *off, uint64_t n, uint64_t base)
+{
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+		off[i] += base;
+}
+} // namespace
+} // namespace pimsnappy
+
+extern "C" snappy_status pim_snappy_gather_shards(int n_shards, const int *devices, const uint8_t *const *d_shard, const uint64_t *bytes,
+                                                  const uint64_t *const *d_shard_off, const uint64_t *nblocks, int dst_device, uint8_t *d_dst,
+                                                  uint64_t *d_dst_off, void *stream)
+{
+	if (n_shards <= 0 || !devices || !d_shard || !bytes || !d_shard_off || !nblocks || !d_dst || !d_dst_off)
+		return SNAPPY_INVALID_INPUT;
+	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	int prev = 0;
+	PIM_CUDA_TRY(cudaGetDevice(&prev));
+	PIM_CUDA_TRY(cudaSetDevice(dst_device));
+	snappy_status rc = SNAPPY_OK;
+	uint64_t base = 0, blk = 0;
+	for (int g = 0; g < n_shards && rc == SNAPPY_OK; g++) {
+		if (devices[g] != dst_device) { // direct peer access if the link allows it; the copies below work either way
+			int can = 0;
+			if (cudaDeviceCanAccessPeer(&can, dst_device, devices[g]) == cudaSuccess && can && cudaDeviceEnablePeerAccess(devices[g], 0) != cudaSuccess)
+				cudaGetLastError(); // already enabled
+		}
+		const bool last = g + 1 == n_shards;
+		const uint64_t nent = nblocks[g] + (last ? 1 : 0); // the closing entry of a shard is the first of the next
+		if (cudaMemcpyPeerAsync(d_dst + base, dst_device, d_shard[g], devices[g], bytes[g], st) != cudaSuccess ||
+		    (nent && cudaMemcpyPeerAsync(d_dst_off + blk, dst_device, d_shard_off[g], devices[g], nent * sizeof(uint64_t), st) != cudaSuccess)) {
+			rc = SNAPPY_INVALID_INPUT;
+			break;
+		}
+		if (nent && base) {
+			rebase_offsets_kernel<<<(unsigned)std::min<uint64_t>(256, (nent + 255) / 256), 256, 0, st>>>(d_dst_off + blk, nent, base);
+			note_launch(1);
+		}
+		base += bytes[g];
+		blk += nblocks[g];
+	}
+	if (rc == SNAPPY_OK && cudaGetLastError() != cudaSuccess)
+		rc = SNAPPY_INVALID_INPUT;
+	cudaSetDevice(prev);
+	return rc;
+}
+
 extern "C" void pim_snappy_set_chunk_bytes(uint64_t bytes) { g_chunk_bytes.store(bytes == ~uint64_t(0) ? bytes - 1 : bytes); }
 
 // ----------------------------------------------------------------------- setup

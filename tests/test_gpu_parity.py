@@ -255,6 +255,48 @@ def test_multi_gpu_shards_match_single_gpu(P, oracle):
         P.set_devices([0])
 
 
+def test_gather_shards_over_peer_copies(P, oracle):
+    """shards compressed on different GPUs, gathered peer to peer into one block stream on GPU 0,
+    which must be the oracle's stream body and decode back on GPU 0."""
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("needs at least two GPUs")
+    L = P.lib()
+    bs = 32768
+    data = P.synth_host(P.SYNTH_MIX, 0x6A7, (6 << 20) + 1234)
+    nb = int(L.pim_snappy_num_blocks(data.size, bs))
+    devs, shards, offs, nbs = list(range(min(ndev, 4))), [], [], []
+    for g in devs:
+        lo, hi = P.shard_range(nb, len(devs), g)
+        part = data[lo * bs:min(data.size, hi * bs)]
+        with torch.cuda.device(g):
+            d_in = torch.from_numpy(part.copy()).to(f"cuda:{g}")
+            scratch = torch.empty(int(L.pim_snappy_compress_scratch_bytes(part.size, bs)), dtype=torch.uint8, device=f"cuda:{g}")
+            d_out = torch.empty(int(L.pim_snappy_compress_bound(part.size, bs)), dtype=torch.uint8, device=f"cuda:{g}")
+            d_off = torch.empty(hi - lo + 1, dtype=torch.int64, device=f"cuda:{g}")
+            P.compress_device(d_in.data_ptr(), part.size, bs, scratch.data_ptr(), scratch.numel(), d_out.data_ptr(), d_off.data_ptr(),
+                              torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+        shards.append(d_out); offs.append(d_off); nbs.append(hi - lo)
+    sizes = [int(o[-1].item()) for o in offs]
+    total = sum(sizes)
+    with torch.cuda.device(0):
+        d_all = torch.zeros(total, dtype=torch.uint8, device="cuda:0")
+        d_all_off = torch.zeros(nb + 1, dtype=torch.int64, device="cuda:0")
+        st = torch.cuda.current_stream().cuda_stream
+        P.gather_shards(devs, [t.data_ptr() for t in shards], sizes, [t.data_ptr() for t in offs], nbs, 0, d_all.data_ptr(), d_all_off.data_ptr(), st)
+        d_back = torch.zeros(data.size, dtype=torch.uint8, device="cuda:0")
+        d_status = torch.ones(1, dtype=torch.int32, device="cuda:0")
+        P.decompress_device(d_all.data_ptr(), d_all_off.data_ptr(), nb, bs, data.size, d_back.data_ptr(), d_status.data_ptr(), st)
+        torch.cuda.synchronize()
+    want = oracle.compress(data, bs)
+    hdr = want.size - total
+    assert hdr > 0 and np.array_equal(d_all.cpu().numpy(), want[hdr:])
+    assert int(d_all_off[-1].item()) == total and int(d_status.item()) == 0
+    assert np.array_equal(d_back.cpu().numpy(), data)
+
+
 def test_cli_matches_reference_contract(P, golden, tmp_path):
     # same lines the reference CLI prints (dpu_snappy.c:152,159,212-227), same round trip as `make test`
     cli = os.path.join(os.path.dirname(P.LIB_PATH), "dpu_snappy")
