@@ -43,7 +43,7 @@ __host__ __device__ inline uint32_t slot_stride(uint32_t block_size)
 constexpr uint32_t MAX_PERSIST_CTAS = 160;
 constexpr uint32_t MAX_GT = 8;
 constexpr uint32_t MAX_PAIRS = 15;   // named barriers 1..15, one per pair
-constexpr uint32_t PAIR_CTL_BYTES = (uint32_t)sizeof(EmitRing) + 4u; // record ring + mail word
+constexpr uint32_t PAIR_CTL_BYTES = (uint32_t)sizeof(EmitRing); // record ring + mail word
 
 // Pairs of one CTA for this block size: n_sm with the table in shared memory, n_gt in global memory.
 inline void plan_pairs(uint32_t block_size, uint32_t smem_budget, uint32_t *n_sm, uint32_t *n_gt)
@@ -133,26 +133,21 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 }
 
 // The persistent CTA: pairs [0, n_sm) keep their table in shared memory, pairs [n_sm, n_sm + n_gt) in gtables.
-__global__ void __launch_bounds__(64 * MAX_PAIRS, 1) snappy_compress_kernel(CompressArgs a, uint8_t *__restrict__ gtables, uint32_t n_sm, uint32_t n_gt)
+__global__ void __launch_bounds__(64 * (MAX_PAIRS + 1), 1) snappy_compress_kernel(CompressArgs a, uint8_t *__restrict__ gtables, uint32_t n_sm, uint32_t n_gt)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
 	// Warp w runs on scheduler w % 4.  The parsers are the busy warps (an emitter mostly waits), so the
 	// roles are laid out in groups of four warps = two pairs: (parser, parser, emitter, emitter) in even
 	// groups and (emitter, emitter, parser, parser) in odd ones -- every scheduler gets its share of parsers.
 	const uint32_t w = threadIdx.x >> 5, g = w >> 2, k = w & 3, npairs = n_sm + n_gt;
-	uint32_t pair, role; // role 0: parser, 1: emitter
-	if (2 * g + 1 < npairs) {
-		const uint32_t kk = (g & 1) ? (k ^ 2u) : k;
-		pair = 2 * g + (kk & 1u);
-		role = kk >> 1;
-	} else { // a last group of one pair
-		pair = 2 * g;
-		role = k & 1u;
-	}
+	const uint32_t kk = (g & 1) ? (k ^ 2u) : k;
+	const uint32_t pair = 2 * g + (kk & 1u), role = kk >> 1; // role 0: parser, 1: emitter
+	if (pair >= npairs) // the CTA is launched with an even number of pair slots
+		return;
 	const uint32_t tbytes = 2u * table_entries(a.block_size);
 	uint8_t *ctl = sm + n_sm * tbytes;
 	EmitRing *ring = reinterpret_cast<EmitRing *>(ctl) + pair;
-	volatile uint32_t *mail = reinterpret_cast<volatile uint32_t *>(ctl + npairs * sizeof(EmitRing)) + pair;
+	volatile uint32_t *mail = reinterpret_cast<volatile uint32_t *>(&ring->rec[0].pad[0]); // (never written by the ring protocol)
 	if (pair < n_sm)
 		compress_pair<false>(a, sm + pair * tbytes, ring, mail, (int)pair + 1, role);
 	else
@@ -302,7 +297,7 @@ snappy_status pimsnappy::compress_device_placed(const uint8_t *d_in, uint64_t in
 	ca.stride = stride;
 	ca.sizes = sizes;
 	ca.counter = counter;
-	snappy_compress_kernel<<<grid, 64 * npairs, smem, st>>>(ca, gtables, n_sm, n_gt);
+	snappy_compress_kernel<<<grid, 64 * ((npairs + 1u) & ~1u), smem, st>>>(ca, gtables, n_sm, n_gt);
 	prof_end(0, st);
 	prof_begin(1, st);
 	scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, nb, d_block_off);

@@ -343,7 +343,7 @@ struct EmitRec {
 	uint32_t lit_from, lit_len;   // literal emitted before the window's elements (len 0: none)
 	uint32_t copy_off, copy_len;  // copy emitted after them (len 0: none)
 	uint32_t done;      // last record of the block
-	uint32_t pad[7];    // (192-byte records: measurably faster than packed ones)
+	uint32_t pad[7];    // (192-byte records: measurably faster than packed ones; pad[0] of record 0 carries the pair's block index)
 };
 
 struct EmitRing {
