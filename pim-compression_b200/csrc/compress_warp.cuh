@@ -46,7 +46,10 @@ namespace pimsnappy {
 
 constexpr uint32_t CW_MAX_TABLE = 16384; // snappy_compress.c:16-17
 constexpr uint32_t CW_MARGIN = 15;       // snappy_compress.c:299
-constexpr int CW_CHAIN_MAX = 24;         // a new pair is resolved in the same pass if its insert lane is <= this
+constexpr int CW_CHAIN_MAX = 24;
+#ifndef PIM_GT_MATCH
+#define PIM_GT_MATCH 1 // global-memory tables: slot sharing inside a pass found with match.any (0: store + read-back, as for shared memory)
+#endif         // a new pair is resolved in the same pass if its insert lane is <= this
 
 #if defined(__CUDACC__)
 __host__ __device__
@@ -97,15 +100,19 @@ PW_FN void in_load128(const CBlock &c, uint32_t pos, uint32_t v[4])
 
 // number of equal leading bytes (0..16) of in[cand..] and the sixteen bytes `cur`; no FLO/BREV
 // (those cost ~40 cycles on the pass's critical path)
-PW_FN uint32_t common_prefix16(const CBlock &c, uint32_t cand, const uint32_t cur[4])
+PW_FN uint32_t prefix16(const uint32_t cwd[4], const uint32_t cur[4])
 {
-	uint32_t cwd[4];
-	in_load128(c, cand, cwd);
 	const uint32_t d0 = cur[0] ^ cwd[0], d1 = cur[1] ^ cwd[1], d2 = cur[2] ^ cwd[2], d3 = cur[3] ^ cwd[3];
 	const uint32_t d = d0 ? d0 : (d1 ? d1 : (d2 ? d2 : d3));
 	const uint32_t base = d0 ? 0u : (d1 ? 4u : (d2 ? 8u : 12u));
 	const uint32_t inword = ((d & 0xFFu) == 0u) + ((d & 0xFFFFu) == 0u) + ((d & 0xFFFFFFu) == 0u);
 	return d ? base + inword : 16u;
+}
+PW_FN uint32_t common_prefix16(const CBlock &c, uint32_t cand, const uint32_t cur[4])
+{
+	uint32_t cwd[4];
+	in_load128(c, cand, cwd);
+	return prefix16(cwd, cur);
 }
 
 // lanes a..b inclusive (empty if b < a); 0 <= a, b <= 31
@@ -488,27 +495,46 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 			// Speculative insert + read-back: a lane that does not read its own position back shares
 			// its slot with another lane of this pass.
 			uint32_t w1 = p;
-			if (valid) {
-				wp::tbl_st<GT>(c.table, h, p);
-				cand = tc;
-				mlen = common_prefix16(c, tc, cur);
-			}
-			wp::syncwarp();
-			if (valid)
-				w1 = wp::tbl_ld<GT>(c.table, h);
-			const uint32_t inval = wp::ballot(!valid);
-			const uint32_t dup1 = wp::ballot(w1 != p);
-			uint32_t same = mybit, lowmask = 0;
-			if (dup1) { // some lanes share a slot: find the groups (a second round tells the winners)
-				CW_STAT(6);
-				uint32_t w2 = p;
-				if (valid && w1 != p)
+			uint32_t same = mybit, lowmask = 0, dup1;
+			bool involved;
+			if (GT && PIM_GT_MATCH) {
+				// Table in global memory: a read-back is one more L2 round trip on the chain.  The lanes that share a
+				// slot are found with match.any instead, which executes while the candidate bytes are on their way.
+				if (valid) {
 					wp::tbl_st<GT>(c.table, h, p);
+					cand = tc;
+				}
+				uint32_t cwd[4];
+				in_load128(c, tc, cwd); // (tc = 0 on lanes that do not probe)
+				same = wp::match_any(valid ? h : 0xFFFFFFFFu);
+				mlen = valid ? prefix16(cwd, cur) : 0u;
+				involved = valid && same != mybit;
+				dup1 = wp::ballot(involved);
+			} else {
+				if (valid) {
+					wp::tbl_st<GT>(c.table, h, p);
+					cand = tc;
+					mlen = common_prefix16(c, tc, cur);
+				}
 				wp::syncwarp();
 				if (valid)
-					w2 = wp::tbl_ld<GT>(c.table, h);
-				const bool involved = valid && (w1 != p || w2 != p);
-				same = wp::match_any(involved ? h : 0xFFFFFFFFu);
+					w1 = wp::tbl_ld<GT>(c.table, h);
+				dup1 = wp::ballot(w1 != p);
+				involved = false;
+			}
+			const uint32_t inval = wp::ballot(!valid);
+			if (dup1) { // some lanes share a slot: find the groups (a second round tells the winners)
+				CW_STAT(6);
+				if (!(GT && PIM_GT_MATCH)) {
+					uint32_t w2 = p;
+					if (valid && w1 != p)
+						wp::tbl_st<GT>(c.table, h, p);
+					wp::syncwarp();
+					if (valid)
+						w2 = wp::tbl_ld<GT>(c.table, h);
+					involved = valid && (w1 != p || w2 != p);
+					same = wp::match_any(involved ? h : 0xFFFFFFFFu);
+				}
 				if (!involved)
 					same = mybit;
 				lowmask = same & lt;

@@ -28,12 +28,17 @@ class Emu:
         L.emu_compress.restype = C.c_uint64
         L.emu_compress.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p]
         L.emu_set_order.argtypes = [C.c_int]
+        L.emu_set_global_table.argtypes = [C.c_int]
         self.L = L
 
     def set_order(self, order: int):
         """Which lane's store lands last when lanes of one instruction hit the same slot (unspecified on the GPU):
         0 = highest lane, 1 = lowest lane, 2 = shuffled."""
         self.L.emu_set_order(order)
+
+    def set_global_table(self, on: bool):
+        """Run the parser variant of the pairs whose hash table lives in global memory (parse_block_warp<true>)."""
+        self.L.emu_set_global_table(1 if on else 0)
 
     def compress(self, data, block_size: int) -> np.ndarray:
         d = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data)

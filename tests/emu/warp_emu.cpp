@@ -44,6 +44,7 @@ bool g_done[NC];
 uint32_t g_slot[NC];
 int g_op[NC];          // which primitive each lane is in (divergence check)
 unsigned g_opseq[NC];  // how many primitives each lane has executed
+int g_global_table = 0; // 1: run parse_block_warp<true>
 int g_order = 0; // 0: lanes run 0..31 between primitives (lane 31's store wins a conflict), 1: 31..0, 2: shuffled
 void (*g_body)(void *) = nullptr;
 void *g_arg = nullptr;
@@ -190,7 +191,10 @@ void body(void *arg)
 {
 	Job *j = static_cast<Job *>(arg);
 	if (g_cur < NL) {
-		pimsnappy::parse_block_warp<false>(j->blk, &j->ring);
+		if (g_global_table)
+			pimsnappy::parse_block_warp<true>(j->blk, &j->ring); // the code path of the pairs whose table lives in global memory
+		else
+			pimsnappy::parse_block_warp<false>(j->blk, &j->ring);
 	} else {
 		const uint32_t r = pimsnappy::emit_block_warp(j->blk, &j->ring);
 		if (pimsnappy::wp::lane() == 0)
@@ -212,6 +216,7 @@ size_t put_varint(uint8_t *p, uint32_t v) // snappy_compress.c:69-98
 } // namespace
 
 extern "C" void emu_set_order(int order) { g_order = order; }
+extern "C" void emu_set_global_table(int on) { g_global_table = on; }
 
 // Compress in[0..len) into out (capacity >= 32 + len + len/6 + 40 * blocks); returns the file size.
 extern "C" uint64_t emu_compress(const uint8_t *in, uint64_t len, uint32_t block_size, uint8_t *out)

@@ -86,3 +86,29 @@ def test_fuzz(emu, oracle, golden):
         assert _same(emu.compress(d, bs), oracle.compress(d, bs)), (i, d.size, bs)
     st = emu.stats()
     assert st[5] > 0 and st[6] > st[5]  # shared-slot passes and serial re-resolves both occurred
+
+
+def test_global_table_variant(emu, oracle, golden):
+    """parse_block_warp<true> (pairs whose hash table lives in global memory: slot sharing inside a pass is found
+    with match.any instead of a store + read-back) gives the same bytes."""
+    text = golden["plrabn12"][0]
+    emu.set_global_table(True)
+    try:
+        for order in (0, 1, 2):
+            emu.set_order(order)
+            for name, data in edge_inputs().items():
+                d = data[:20000]
+                for bs in (32768, 1000):
+                    assert _same(emu.compress(d, bs), oracle.compress(d, bs)), (name, bs, order)
+        rng = np.random.default_rng(7771)
+        for i in range(150):
+            d = _fuzz_case(rng, text)
+            bs = int(rng.choice([int(rng.integers(1, 70)), int(rng.integers(70, 3000)), 4096, 32768]))
+            emu.set_order(i % 3)
+            assert _same(emu.compress(d, bs), oracle.compress(d, bs)), (i, d.size, bs)
+        txt, sn = golden["terror2"]
+        assert _same(emu.compress(txt, 32768), sn)
+        st = emu.stats()
+        assert st[6] > 0  # shared-slot passes occurred
+    finally:
+        emu.set_global_table(False)
