@@ -158,6 +158,21 @@ snappy_status pim_snappy_decompress_device(const uint8_t *d_comp, const uint64_t
                                            uint64_t nblocks, uint32_t block_size, uint64_t out_len,
                                            uint8_t *d_out, uint32_t *d_status, void *stream);
 
+/* The same for n_streams independent streams at once (callers whose data already lives in HBM
+ * hand over a batch instead of one slurped file, cf. read_input_host, dpu_snappy.c:23-50).  All arrays are HOST
+ * arrays of n_streams entries holding device pointers / sizes; stream i uses exactly the arguments
+ * pim_snappy_compress_device() would take for it (its own scratch, output and offset buffers) and gets exactly
+ * the same bytes.  Up to 32 streams share ONE compress (decompress) kernel launch whose CTAs pull blocks of all
+ * streams from one queue, so the GPU does not drain and refill between streams; larger batches take one launch
+ * per 32 streams.  d_status: device u32[n_streams], one word per stream (zeroed by the call, OR-ed with 1 if a
+ * block of that stream is malformed).  Asynchronous on `stream`. */
+snappy_status pim_snappy_compress_batch_device(int n_streams, const uint8_t *const *d_in, const uint64_t *input_len, uint32_t block_size,
+                                               uint8_t *const *d_scratch, const uint64_t *scratch_bytes, uint8_t *const *d_out,
+                                               uint64_t *const *d_block_off, void *stream);
+snappy_status pim_snappy_decompress_batch_device(int n_streams, const uint8_t *const *d_comp, const uint64_t *const *d_block_off,
+                                                 const uint64_t *nblocks, uint32_t block_size, const uint64_t *out_len,
+                                                 uint8_t *const *d_out, uint32_t *d_status, void *stream);
+
 /* One contiguous block stream on ONE GPU from shards that were compressed on several GPUs
  * (the device-side form of the host stitch, snappy_compress.c:697-703).
  * Shard g, in block order, lives on device devices[g]: d_shard[g] = its block stream of bytes[g]

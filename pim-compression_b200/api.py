@@ -78,6 +78,10 @@ def lib() -> C.CDLL:
         "pim_snappy_compress_scratch_bytes": (C.c_uint64, [C.c_uint64, C.c_uint32]),
         "pim_snappy_compress_device": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
         "pim_snappy_decompress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
+        "pim_snappy_compress_batch_device": (C.c_int, [C.c_int, P(C.c_void_p), P(C.c_uint64), C.c_uint32, P(C.c_void_p), P(C.c_uint64), P(C.c_void_p),
+                                                       P(C.c_void_p), C.c_void_p]),
+        "pim_snappy_decompress_batch_device": (C.c_int, [C.c_int, P(C.c_void_p), P(C.c_void_p), P(C.c_uint64), C.c_uint32, P(C.c_uint64), P(C.c_void_p),
+                                                         C.c_void_p, C.c_void_p]),
         "pim_snappy_gather_shards": (C.c_int, [C.c_int, P(C.c_int), P(C.c_void_p), P(C.c_uint64), P(C.c_void_p), P(C.c_uint64), C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_void_p]),
         "pim_snappy_launch_count": (C.c_uint64, []),
@@ -99,7 +103,8 @@ EXPORTED_SYMBOLS = [
     "setup_compression", "setup_decompression", "snappy_compress_dpu", "snappy_decompress_dpu",
     "snappy_compress_gpu", "snappy_decompress_gpu", "get_runtime", "pim_snappy_host_alloc", "pim_snappy_host_free",
     "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_set_chunk_bytes", "pim_snappy_shard_range", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
-    "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_decompress_device", "pim_snappy_gather_shards",
+    "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_decompress_device", "pim_snappy_compress_batch_device",
+    "pim_snappy_decompress_batch_device", "pim_snappy_gather_shards",
     "pim_snappy_launch_count", "pim_snappy_profile", "pim_snappy_profile_read", "pim_snappy_synth_host", "pim_snappy_synth_device", "pim_snappy_version",
 ]
 
@@ -253,6 +258,24 @@ def compress_device(d_in_ptr: int, n: int, block_size: int, d_scratch_ptr: int, 
     st = lib().pim_snappy_compress_device(d_in_ptr, n, block_size, d_scratch_ptr, scratch_bytes, d_out_ptr, d_off_ptr, stream)
     if st != SNAPPY_OK:
         raise SnappyError(st, "pim_snappy_compress_device")
+
+
+def compress_batch_device(d_in_ptrs, lens, block_size: int, d_scratch_ptrs, scratch_bytes, d_out_ptrs, d_off_ptrs, stream: int = 0) -> None:
+    """pim_snappy_compress_batch_device: several device-resident streams in one compress launch."""
+    n = len(d_in_ptrs)
+    st = lib().pim_snappy_compress_batch_device(n, (C.c_void_p * n)(*d_in_ptrs), (C.c_uint64 * n)(*lens), block_size, (C.c_void_p * n)(*d_scratch_ptrs),
+                                                (C.c_uint64 * n)(*scratch_bytes), (C.c_void_p * n)(*d_out_ptrs), (C.c_void_p * n)(*d_off_ptrs), stream)
+    if st != SNAPPY_OK:
+        raise SnappyError(st, "pim_snappy_compress_batch_device")
+
+
+def decompress_batch_device(d_comp_ptrs, d_off_ptrs, nblocks, block_size: int, out_lens, d_out_ptrs, d_status_ptr: int, stream: int = 0) -> None:
+    """pim_snappy_decompress_batch_device: several block streams in one decompress launch; d_status: one u32 per stream."""
+    n = len(d_comp_ptrs)
+    st = lib().pim_snappy_decompress_batch_device(n, (C.c_void_p * n)(*d_comp_ptrs), (C.c_void_p * n)(*d_off_ptrs), (C.c_uint64 * n)(*nblocks), block_size,
+                                                  (C.c_uint64 * n)(*out_lens), (C.c_void_p * n)(*d_out_ptrs), d_status_ptr, stream)
+    if st != SNAPPY_OK:
+        raise SnappyError(st, "pim_snappy_decompress_batch_device")
 
 
 def gather_shards(devices, shard_ptrs, shard_bytes, off_ptrs, nblocks, dst_device: int, d_dst_ptr: int, d_dst_off_ptr: int, stream: int = 0) -> None:

@@ -25,6 +25,10 @@ void prof_end(int which, cudaStream_t st);
 // The streamed host path passes false: several group kernels share the SMs there.
 snappy_status compress_device_placed(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch, uint64_t scratch_bytes,
                                      uint8_t *d_out, uint64_t *d_block_off, cudaStream_t st, bool alone_on_gpu);
+// the same for up to 32 streams in one compress launch (pim_snappy_compress_batch_device)
+snappy_status compress_batch_placed(int n_streams, const uint8_t *const *d_in, const uint64_t *input_len, uint32_t block_size,
+                                    uint8_t *const *d_scratch, const uint64_t *scratch_bytes, uint8_t *const *d_out,
+                                    uint64_t *const *d_block_off, cudaStream_t st, bool alone_on_gpu);
 
 // ---- shared-memory byte-addressed access -----------------------------------
 // All kernels address their dynamic shared memory as one byte array `sm` and

@@ -24,6 +24,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 #include "compress_warp.cuh"
@@ -71,14 +72,23 @@ __host__ __device__ inline uint64_t gtable_bytes(uint32_t block_size) { return (
 #define PIM_PAIR_INLINE __forceinline__
 #endif
 
-struct CompressArgs {
+// One launch compresses up to MAX_BATCH streams (pim_snappy_compress_batch_device): the pairs pull block indices of the
+// concatenation of the streams' blocks from one counter, so no SM idles between streams.
+constexpr uint32_t MAX_BATCH = 32;
+struct StreamArgs {
 	const uint8_t *in;
 	uint64_t in_len;
-	uint32_t block_size, nblocks;
-	const uint8_t *tail_copy;
+	const uint8_t *tail_copy; // the stream's last block with readable slack behind it
 	uint8_t *slots;
-	uint32_t stride;
 	uint32_t *sizes;
+	uint32_t first_blk;       // index of the stream's first block in the batch
+	uint32_t nblocks;
+};
+struct CompressArgs {
+	StreamArgs s[MAX_BATCH];
+	uint32_t n_streams;
+	uint32_t block_size, nblocks; // nblocks: of the whole batch
+	uint32_t stride;
 	uint32_t *counter;
 };
 
@@ -95,12 +105,17 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 		if (ptid == 0)
 			*mail = atomicAdd(a.counter, 1u);
 		bar_sync(bar_id, 64);
-		const uint32_t blk = *mail;
-		if (blk >= a.nblocks)
+		const uint32_t gblk = *mail;
+		if (gblk >= a.nblocks)
 			break;
+		uint32_t si = 0; // the stream this block belongs to (streams are in block order)
+		while (si + 1 < a.n_streams && gblk >= a.s[si + 1].first_blk)
+			si++;
+		const StreamArgs &sa = a.s[si];
+		const uint32_t blk = gblk - sa.first_blk;
 		const uint64_t in_off = blk * (uint64_t)a.block_size;
-		const uint32_t n = (uint32_t)min((uint64_t)a.block_size, a.in_len - in_off);
-		const uint8_t *gsrc = blk + 1 == a.nblocks ? a.tail_copy : a.in + in_off;
+		const uint32_t n = (uint32_t)min((uint64_t)a.block_size, sa.in_len - in_off);
+		const uint8_t *gsrc = blk + 1 == sa.nblocks ? sa.tail_copy : sa.in + in_off;
 		const uint32_t ts = table_entries(n);
 
 		CBlock c;
@@ -108,7 +123,7 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 		c.inw = reinterpret_cast<const uint32_t *>(gsrc - c.mis);
 		c.table = reinterpret_cast<uint16_t *>(tbytes);
 		c.shift = 32 - (31 - __clz(ts)); // snappy_compress.c:288
-		c.out = a.slots + blk * (uint64_t)a.stride;
+		c.out = sa.slots + blk * (uint64_t)a.stride;
 		c.n = n;
 
 		for (uint32_t i = ptid * 128u; i < n; i += 64u * 128u) // HBM -> L2 for the whole block, ahead of the parse
@@ -126,14 +141,14 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 		} else { // output bytes only
 			const uint32_t o = emit_block_warp(c, ring);
 			if (lane == 0)
-				a.sizes[blk] = o;
+				sa.sizes[blk] = o;
 		}
 		bar_sync(bar_id, 64); // table, ring and mail are reused
 	}
 }
 
 // The persistent CTA: pairs [0, n_sm) keep their table in shared memory, pairs [n_sm, n_sm + n_gt) in gtables.
-__global__ void __launch_bounds__(64 * (MAX_PAIRS + 1), 1) snappy_compress_kernel(CompressArgs a, uint8_t *__restrict__ gtables, uint32_t n_sm, uint32_t n_gt)
+__global__ void __launch_bounds__(64 * (MAX_PAIRS + 1), 1) snappy_compress_kernel(const __grid_constant__ CompressArgs a, uint8_t *__restrict__ gtables, uint32_t n_sm, uint32_t n_gt)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
 	// Warp w runs on scheduler w % 4.  The parsers are the busy warps (an emitter mostly waits), so the
@@ -239,26 +254,79 @@ extern "C" snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_
 snappy_status pimsnappy::compress_device_placed(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_scratch,
                                                 uint64_t scratch_bytes, uint8_t *d_out, uint64_t *d_block_off, cudaStream_t st, bool alone_on_gpu)
 {
+	return compress_batch_placed(1, &d_in, &input_len, block_size, &d_scratch, &scratch_bytes, &d_out, &d_block_off, st, alone_on_gpu);
+}
+
+extern "C" snappy_status pim_snappy_compress_batch_device(int n_streams, const uint8_t *const *d_in, const uint64_t *input_len, uint32_t block_size,
+                                                          uint8_t *const *d_scratch, const uint64_t *scratch_bytes, uint8_t *const *d_out,
+                                                          uint64_t *const *d_block_off, void *stream)
+{
+	if (n_streams < 0)
+		return SNAPPY_INVALID_INPUT;
+	for (int at = 0; at < n_streams; at += (int)MAX_BATCH) { // one launch per MAX_BATCH streams
+		const int k = std::min<int>((int)MAX_BATCH, n_streams - at);
+		const snappy_status r = compress_batch_placed(k, d_in + at, input_len + at, block_size, d_scratch + at, scratch_bytes + at, d_out + at,
+		                                              d_block_off + at, static_cast<cudaStream_t>(stream), true);
+		if (r != SNAPPY_OK)
+			return r;
+	}
+	return SNAPPY_OK;
+}
+
+// Streams [0, n_streams) (n_streams <= MAX_BATCH) in ONE compress launch, then one size scan + compaction per stream.
+snappy_status pimsnappy::compress_batch_placed(int n_streams, const uint8_t *const *d_in, const uint64_t *input_len, uint32_t block_size,
+                                               uint8_t *const *d_scratch, const uint64_t *scratch_bytes, uint8_t *const *d_out,
+                                               uint64_t *const *d_block_off, cudaStream_t st, bool alone_on_gpu)
+{
 	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE)
 		return SNAPPY_BUFFER_TOO_SMALL;
-	const uint64_t nb = pim_snappy_num_blocks(input_len, block_size);
-	if (nb > 0x7FFFFFFFull || scratch_bytes < pim_snappy_compress_scratch_bytes(input_len, block_size))
-		return SNAPPY_BUFFER_TOO_SMALL;
-	if (nb == 0) {
-		PIM_CUDA_TRY(cudaMemsetAsync(d_block_off, 0, sizeof(uint64_t), st));
-		return SNAPPY_OK;
-	}
-	uint32_t *sizes = reinterpret_cast<uint32_t *>(d_scratch);
-	uint32_t *counter = reinterpret_cast<uint32_t *>(d_scratch + ((nb * 4 + 255) & ~255ull));
-	uint8_t *tail_copy = reinterpret_cast<uint8_t *>(counter) + 256;
-	uint8_t *gtables = tail_copy + tail_copy_bytes(block_size);
-	uint8_t *slots = gtables + gtable_bytes(block_size);
-	PIM_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
-	// the stream's last block, with readable slack behind it (same 4-byte phase as in the stream)
-	const uint64_t last_off = (nb - 1) * (uint64_t)block_size;
-	tail_copy += reinterpret_cast<uintptr_t>(d_in + last_off) & 15u;
-	PIM_CUDA_TRY(cudaMemcpyAsync(tail_copy, d_in + last_off, input_len - last_off, cudaMemcpyDeviceToDevice, st));
+	if (n_streams < 0 || n_streams > (int)MAX_BATCH)
+		return SNAPPY_INVALID_INPUT;
 	const uint32_t stride = slot_stride(block_size);
+	CompressArgs ca;
+	memset(&ca, 0, sizeof(ca));
+	ca.block_size = block_size;
+	ca.stride = stride;
+	uint8_t *gtables = nullptr;
+	uint64_t total = 0;
+	int idx[MAX_BATCH]; // streams with blocks, in order
+	for (int i = 0; i < n_streams; i++) {
+		const uint64_t nb = pim_snappy_num_blocks(input_len[i], block_size);
+		if (nb > 0x7FFFFFFFull || total + nb > 0x7FFFFFFFull || scratch_bytes[i] < pim_snappy_compress_scratch_bytes(input_len[i], block_size))
+			return SNAPPY_BUFFER_TOO_SMALL;
+		if (nb == 0) {
+			PIM_CUDA_TRY(cudaMemsetAsync(d_block_off[i], 0, sizeof(uint64_t), st));
+			continue;
+		}
+		uint32_t *sizes = reinterpret_cast<uint32_t *>(d_scratch[i]);
+		uint32_t *counter = reinterpret_cast<uint32_t *>(d_scratch[i] + ((nb * 4 + 255) & ~255ull));
+		uint8_t *tail_copy = reinterpret_cast<uint8_t *>(counter) + 256;
+		uint8_t *gt = tail_copy + tail_copy_bytes(block_size);
+		uint8_t *slots = gt + gtable_bytes(block_size);
+		if (!gtables) { // the batch's counter and global-memory hash tables are those of its first stream
+			gtables = gt;
+			ca.counter = counter;
+			PIM_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
+		}
+		// the stream's last block, with readable slack behind it (same 4-byte phase as in the stream)
+		const uint64_t last_off = (nb - 1) * (uint64_t)block_size;
+		tail_copy += reinterpret_cast<uintptr_t>(d_in[i] + last_off) & 15u;
+		PIM_CUDA_TRY(cudaMemcpyAsync(tail_copy, d_in[i] + last_off, input_len[i] - last_off, cudaMemcpyDeviceToDevice, st));
+		StreamArgs &sa = ca.s[ca.n_streams];
+		sa.in = d_in[i];
+		sa.in_len = input_len[i];
+		sa.tail_copy = tail_copy;
+		sa.slots = slots;
+		sa.sizes = sizes;
+		sa.first_blk = (uint32_t)total;
+		sa.nblocks = (uint32_t)nb;
+		idx[ca.n_streams++] = i;
+		total += nb;
+	}
+	if (total == 0)
+		return SNAPPY_OK;
+	ca.nblocks = (uint32_t)total;
+	const uint64_t nb = total;
 
 	static int smem_optin[64] = {0}; // per device: opt-in shared memory per CTA
 	static int sm_count[64] = {0};
@@ -287,25 +355,18 @@ snappy_status pimsnappy::compress_device_placed(const uint8_t *d_in, uint64_t in
 	const uint32_t smem = n_sm * 2u * table_entries(block_size) + npairs * PAIR_CTL_BYTES + 16u;
 	const unsigned grid = (unsigned)std::min<uint64_t>(ctas_max, (nb + npairs - 1) / npairs);
 	prof_begin(0, st);
-	CompressArgs ca;
-	ca.in = d_in;
-	ca.in_len = input_len;
-	ca.block_size = block_size;
-	ca.nblocks = (uint32_t)nb;
-	ca.tail_copy = tail_copy;
-	ca.slots = slots;
-	ca.stride = stride;
-	ca.sizes = sizes;
-	ca.counter = counter;
 	snappy_compress_kernel<<<grid, 64 * ((npairs + 1u) & ~1u), smem, st>>>(ca, gtables, n_sm, n_gt);
 	prof_end(0, st);
-	prof_begin(1, st);
-	scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, nb, d_block_off);
-	prof_end(1, st);
-	prof_begin(2, st);
-	compact_kernel<<<(unsigned)nb, 128, 0, st>>>(slots, stride, sizes, d_block_off, d_out);
-	prof_end(2, st);
-	note_launch(3);
+	for (uint32_t k = 0; k < ca.n_streams; k++) {
+		const StreamArgs &sa = ca.s[k];
+		prof_begin(1, st);
+		scan_sizes_kernel<<<1, 1024, 0, st>>>(sa.sizes, sa.nblocks, d_block_off[idx[k]]);
+		prof_end(1, st);
+		prof_begin(2, st);
+		compact_kernel<<<sa.nblocks, 128, 0, st>>>(sa.slots, stride, sa.sizes, d_block_off[idx[k]], d_out[idx[k]]);
+		prof_end(2, st);
+	}
+	note_launch(1 + 2 * ca.n_streams);
 	PIM_CUDA_TRY(cudaGetLastError());
 	return SNAPPY_OK;
 }

@@ -26,6 +26,8 @@
 //
 // Element formats: snappy/README.md:19-33, snappy_decompress.c:244-283, dpu_snappy.h:10-13.
 
+#include <cstring>
+
 #include "common.cuh"
 
 namespace pimsnappy {
@@ -632,11 +634,26 @@ __device__ __forceinline__ void decode_block(Dec &d)
 
 // ---------------------------------------------------------------------------
 // Kernel: persistent CTAs of WARPS independent warps; warp g of the grid decodes blocks
-// g, g + total_warps, ...
+// g, g + total_warps, ... of the concatenation of the batch's streams' blocks (one launch decodes up to
+// DEC_MAX_BATCH streams, pim_snappy_decompress_batch_device, so that no SM idles between streams).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_kernel(const uint8_t *__restrict__ comp, const uint64_t *__restrict__ block_off,
-                                                                          uint64_t nblocks, uint32_t block_size, uint64_t out_len,
-                                                                          uint8_t *__restrict__ out, uint32_t *__restrict__ status)
+constexpr uint32_t DEC_MAX_BATCH = 32;
+struct DecStream {
+	const uint8_t *comp;
+	const uint64_t *block_off;
+	uint8_t *out;
+	uint64_t out_len;
+	uint64_t first_blk; // index of the stream's first block in the batch
+};
+struct DecArgs {
+	DecStream s[DEC_MAX_BATCH];
+	uint32_t n_streams;
+	uint32_t block_size;
+	uint64_t nblocks;   // of the whole batch
+	uint32_t *status;   // one word per stream
+};
+
+__global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_kernel(const __grid_constant__ DecArgs a)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
 	const int lane = lane_id();
@@ -654,19 +671,23 @@ __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_ke
 	d.ws = sm + SM_WARP0 + warp * WS_BYTES;
 	d.lane = lane;
 	const uint64_t total_warps = (uint64_t)gridDim.x * WARPS;
-	bool any_err = false;
-	for (uint64_t blk = (uint64_t)blockIdx.x * WARPS + warp; blk < nblocks; blk += total_warps) {
-		const uint64_t off0 = block_off[blk], off1 = block_off[blk + 1];
-		const uint64_t out_off = blk * (uint64_t)block_size;
-		d.out_size = (uint32_t)min((uint64_t)block_size, out_len - out_off);
-		d.gdst = out + out_off;
+	uint32_t si = 0; // stream of the current block (block indices only grow)
+	for (uint64_t gblk = (uint64_t)blockIdx.x * WARPS + warp; gblk < a.nblocks; gblk += total_warps) {
+		while (si + 1 < a.n_streams && gblk >= a.s[si + 1].first_blk)
+			si++;
+		const DecStream &ds = a.s[si];
+		const uint64_t blk = gblk - ds.first_blk;
+		const uint64_t off0 = ds.block_off[blk], off1 = ds.block_off[blk + 1];
+		const uint64_t out_off = blk * (uint64_t)a.block_size;
+		d.out_size = (uint32_t)min((uint64_t)a.block_size, ds.out_len - out_off);
+		d.gdst = ds.out + out_off;
 		d.g15 = (uint32_t)(reinterpret_cast<uintptr_t>(d.gdst) & 15u);
-		d.gcomp = comp + off0 + 4;
+		d.gcomp = ds.comp + off0 + 4;
 		d.err = false;
 		bool header_ok = off1 >= off0 + 5; // 4-byte size + at least one element byte
 		d.csize = 0;
 		if (header_ok) {
-			const uint8_t *h = comp + off0;
+			const uint8_t *h = ds.comp + off0;
 			d.csize = (uint32_t)__ldg(h) | ((uint32_t)__ldg(h + 1) << 8) | ((uint32_t)__ldg(h + 2) << 16) | ((uint32_t)__ldg(h + 3) << 24);
 			header_ok = (uint64_t)d.csize + 4 == off1 - off0;
 		}
@@ -674,11 +695,10 @@ __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_ke
 			decode_block(d);
 		else
 			d.err = true;
-		any_err = any_err || __any_sync(FULL, d.err);
+		if (__any_sync(FULL, d.err) && lane == 0)
+			atomicOr(a.status + si, 1u);
 		__syncwarp();
 	}
-	if (any_err && lane == 0)
-		atomicOr(status, 1u);
 }
 
 } // namespace
@@ -686,18 +706,21 @@ __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_ke
 
 using namespace pimsnappy;
 
-extern "C" snappy_status pim_snappy_decompress_device(const uint8_t *d_comp, const uint64_t *d_block_off, uint64_t nblocks,
-                                                      uint32_t block_size, uint64_t out_len, uint8_t *d_out, uint32_t *d_status,
-                                                      void *stream)
+extern "C" snappy_status pim_snappy_decompress_batch_device(int n_streams, const uint8_t *const *d_comp, const uint64_t *const *d_block_off,
+                                                            const uint64_t *nblocks, uint32_t block_size, const uint64_t *out_len,
+                                                            uint8_t *const *d_out, uint32_t *d_status, void *stream)
 {
 	cudaStream_t st = static_cast<cudaStream_t>(stream);
 	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE)
 		return SNAPPY_BUFFER_TOO_SMALL;
-	if (nblocks != pim_snappy_num_blocks(out_len, block_size) || nblocks > 0x7FFFFFFFull)
+	if (n_streams < 0)
 		return SNAPPY_INVALID_INPUT;
-	PIM_CUDA_TRY(cudaMemsetAsync(d_status, 0, sizeof(uint32_t), st));
-	if (nblocks == 0)
+	for (int i = 0; i < n_streams; i++)
+		if (nblocks[i] != pim_snappy_num_blocks(out_len[i], block_size) || nblocks[i] > 0x7FFFFFFFull)
+			return SNAPPY_INVALID_INPUT;
+	if (n_streams == 0)
 		return SNAPPY_OK;
+	PIM_CUDA_TRY(cudaMemsetAsync(d_status, 0, sizeof(uint32_t) * (size_t)n_streams, st));
 	static int max_ctas[64] = {0}; // per device: resident CTAs of the whole GPU
 	int dev = 0;
 	PIM_CUDA_TRY(cudaGetDevice(&dev));
@@ -711,12 +734,39 @@ extern "C" snappy_status pim_snappy_decompress_device(const uint8_t *d_comp, con
 		PIM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 		max_ctas[dev] = per_sm * sms > 0 ? per_sm * sms : 1;
 	}
-	const uint64_t want = (nblocks + WARPS - 1) / WARPS;
-	const unsigned grid = (unsigned)(want < (uint64_t)max_ctas[dev] ? want : (uint64_t)max_ctas[dev]);
-	prof_begin(3, st);
-	snappy_decompress_kernel<<<grid, 32 * WARPS, SMEM_BYTES, st>>>(d_comp, d_block_off, nblocks, block_size, out_len, d_out, d_status);
-	prof_end(3, st);
-	note_launch();
+	for (int at = 0; at < n_streams; at += (int)DEC_MAX_BATCH) { // one launch per DEC_MAX_BATCH streams
+		DecArgs da;
+		memset(&da, 0, sizeof(da));
+		da.block_size = block_size;
+		da.status = d_status + at;
+		uint64_t total = 0;
+		const int k = n_streams - at < (int)DEC_MAX_BATCH ? n_streams - at : (int)DEC_MAX_BATCH;
+		for (int i = 0; i < k; i++) { // (streams without blocks keep their slot: status words are indexed by stream)
+			DecStream &ds = da.s[da.n_streams++];
+			ds.comp = d_comp[at + i];
+			ds.block_off = d_block_off[at + i];
+			ds.out = d_out[at + i];
+			ds.out_len = out_len[at + i];
+			ds.first_blk = total;
+			total += nblocks[at + i];
+		}
+		if (total == 0)
+			continue;
+		da.nblocks = total;
+		const uint64_t want = (total + WARPS - 1) / WARPS;
+		const unsigned grid = (unsigned)(want < (uint64_t)max_ctas[dev] ? want : (uint64_t)max_ctas[dev]);
+		prof_begin(3, st);
+		snappy_decompress_kernel<<<grid, 32 * WARPS, SMEM_BYTES, st>>>(da);
+		prof_end(3, st);
+		note_launch();
+	}
 	PIM_CUDA_TRY(cudaGetLastError());
 	return SNAPPY_OK;
+}
+
+extern "C" snappy_status pim_snappy_decompress_device(const uint8_t *d_comp, const uint64_t *d_block_off, uint64_t nblocks,
+                                                      uint32_t block_size, uint64_t out_len, uint8_t *d_out, uint32_t *d_status,
+                                                      void *stream)
+{
+	return pim_snappy_decompress_batch_device(1, &d_comp, &d_block_off, &nblocks, block_size, &out_len, &d_out, d_status, stream);
 }

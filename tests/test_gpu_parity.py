@@ -174,6 +174,54 @@ def test_device_resident_api_and_generators(P, oracle):
     assert int(d_status.item()) == 0 and torch.equal(d_back, d_in)
 
 
+def test_batch_api_matches_oracle_per_stream(P, oracle):
+    """pim_snappy_compress_batch_device / pim_snappy_decompress_batch_device: ragged streams -- empty, one
+    byte, shorter than a block, text / random / binary -- through ONE launch give, per stream, the oracle's bytes and
+    offsets, and decode back; a malformed stream is reported in its own status word only.  40 streams also cover the
+    split into launches of 32."""
+    import torch
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    L = P.lib()
+    for bs in (32768, 4096):
+        lens = [0, 1, 14, 15, bs - 1, bs, bs + 1, 3 * bs + 17, (2 << 20) + 5, 700001] + [50000 + 977 * i for i in range(30)]
+        hosts = [P.synth_host((P.SYNTH_TEXT, P.SYNTH_RANDOM, P.SYNTH_MIX, P.SYNTH_BIN)[i % 4], 0xBA7C0 + i, n) for i, n in enumerate(lens)]
+        d_in = [torch.from_numpy(h.copy()).to(dev) if h.size else torch.empty(0, dtype=torch.uint8, device=dev) for h in hosts]
+        nbs = [int(L.pim_snappy_num_blocks(n, bs)) for n in lens]
+        scr = [torch.empty(int(L.pim_snappy_compress_scratch_bytes(n, bs)), dtype=torch.uint8, device=dev) for n in lens]
+        outs = [torch.empty(int(L.pim_snappy_compress_bound(n, bs)), dtype=torch.uint8, device=dev) for n in lens]
+        offs = [torch.empty(nb + 1, dtype=torch.int64, device=dev) for nb in nbs]
+        P.compress_batch_device([t.data_ptr() for t in d_in], lens, bs, [t.data_ptr() for t in scr], [t.numel() for t in scr],
+                                [t.data_ptr() for t in outs], [t.data_ptr() for t in offs], st)
+        torch.cuda.synchronize()
+        for i, h in enumerate(hosts):
+            want = oracle.compress(h, bs)
+            hlen, dlen, bs2, woff = P.block_offsets(want)
+            off = offs[i].cpu().numpy().astype(np.uint64)
+            assert np.array_equal(off, woff), (bs, i)
+            assert np.array_equal(outs[i][: int(off[-1])].cpu().numpy(), want[hlen:]), (bs, i)
+        backs = [torch.zeros(n, dtype=torch.uint8, device=dev) for n in lens]
+        status = torch.ones(len(lens), dtype=torch.int32, device=dev)
+        args = ([t.data_ptr() for t in outs], [t.data_ptr() for t in offs], nbs, bs, lens, [t.data_ptr() for t in backs], status.data_ptr(), st)
+        P.decompress_batch_device(*args)
+        torch.cuda.synchronize()
+        assert int(status.abs().sum().item()) == 0
+        for i in range(len(lens)):
+            assert torch.equal(backs[i], d_in[i]), (bs, i)
+        # corrupt one element byte of stream 8 (a copy offset becomes 0xFFFF) -> only its status word is set
+        victim = 8
+        bad = outs[victim].clone()
+        raw = bad[: int(offs[victim][-1].item())].cpu().numpy()
+        raw[4:40] = 0xFE  # copy-2 tags with offset 0xFEFE at the block start: reaches before the block
+        bad[: raw.size] = torch.from_numpy(raw).to(dev)
+        ptrs = list(args[0])
+        ptrs[victim] = bad.data_ptr()
+        P.decompress_batch_device(ptrs, *args[1:])
+        torch.cuda.synchronize()
+        stv = status.cpu().numpy()
+        assert stv[victim] == 1 and int(np.abs(stv).sum()) == 1, stv
+
+
 def test_large_roundtrip_properties(P):
     """BASELINE-size property test (no oracle): 1 GiB mixed stream, compress -> decompress == input,
     block offsets consistent, result independent of how the work is repeated (determinism)."""
