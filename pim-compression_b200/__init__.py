@@ -25,6 +25,8 @@ from .api import (  # noqa: F401
     compress,
     decompress,
     compress_device,
+    compress_batch_device,
+    decompress_batch_device,
     decompress_device,
     gather_shards,
     block_offsets,
