@@ -499,11 +499,10 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 			bool involved;
 			if (GT && PIM_GT_MATCH) {
 				// Table in global memory: a read-back is one more L2 round trip on the chain.  The lanes that share a
-				// slot are found with match.any instead, which executes while the candidate bytes are on their way.
-				if (valid) {
-					wp::tbl_st<GT>(c.table, h, p);
+				// slot are found with match.any instead, which executes while the candidate bytes are on their way,
+				// and nothing is stored speculatively: the inserted lanes write their slots once the pass is resolved.
+				if (valid)
 					cand = tc;
-				}
 				uint32_t cwd[4];
 				in_load128(c, tc, cwd); // (tc = 0 on lanes that do not probe)
 				same = wp::match_any(valid ? h : 0xFFFFFFFFu);
@@ -577,7 +576,10 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 				CW_STAT(3);
 
 			// ---- table: undo the speculative inserts of lanes that were not inserted -----------
-			if (w.outcome != 2) {
+			if (GT && PIM_GT_MATCH) { // (nothing was stored yet: the last inserted lane of every slot writes it)
+				if (w.outcome != 2 && valid && inI && !(same & Imask & ~le))
+					wp::tbl_st<GT>(c.table, h, p);
+			} else if (w.outcome != 2) {
 				if (valid && !inI)
 					wp::tbl_st<GT>(c.table, h, tc);
 				if (dup1) { // shared slots: the last inserted lane of the group owns the slot
