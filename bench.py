@@ -194,8 +194,7 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's banner / debug lines off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
     L = P.lib()
     assert P.set_devices([local_rank]) == 1, "no usable sm_100 GPU"
