@@ -191,10 +191,14 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # Library banners (NCCL prints its version on stdout at communicator creation) go to stderr: file descriptor 1 points at
+    # stderr until the JSON line is printed, so that stdout carries exactly that one line.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist = None
     if world > 1:
         import torch.distributed as dist
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's banner / debug lines off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
     L = P.lib()
     assert P.set_devices([local_rank]) == 1, "no usable sm_100 GPU"
@@ -399,7 +403,10 @@ def run_ours(args):
                            "compressed_fraction": comp_bytes / U, "bytes_per_gpu": U},
                 "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks}
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     if dist is not None:
         dist.destroy_process_group()
     return 0
