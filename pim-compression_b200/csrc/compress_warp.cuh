@@ -46,10 +46,13 @@ namespace pimsnappy {
 
 constexpr uint32_t CW_MAX_TABLE = 16384; // snappy_compress.c:16-17
 constexpr uint32_t CW_MARGIN = 15;       // snappy_compress.c:299
-constexpr int CW_CHAIN_MAX = 24;
+#ifndef PIM_CW_CHAIN_MAX
+#define PIM_CW_CHAIN_MAX 30 // (30 = as long as a continuation lane exists; measured on B200, text: 20: 34.4, 24: 37.6, 28: 40.2, 30: 41.2 GB/s)
+#endif
+constexpr int CW_CHAIN_MAX = PIM_CW_CHAIN_MAX; // a new pair is resolved in the same pass if its insert lane is <= this
 #ifndef PIM_GT_MATCH
 #define PIM_GT_MATCH 1 // global-memory tables: slot sharing inside a pass found with match.any (0: store + read-back, as for shared memory)
-#endif         // a new pair is resolved in the same pass if its insert lane is <= this
+#endif
 
 #if defined(__CUDACC__)
 __host__ __device__
