@@ -51,7 +51,12 @@ constexpr uint32_t TAIL = 80;            // staged look-ahead past the chunk (ta
 constexpr uint32_t STAGE_BYTES = CHUNK + TAIL + 16;
 constexpr uint32_t MAX_REC = CHUNK / 2;  // an element occupies >= 2 compressed bytes
 constexpr uint32_t SHORT_LIT = 60;       // literals up to this long are served from the staged bytes
-constexpr uint32_t RUNAHEAD = RING / 4;  // the window stops fetching when this far ahead of the frontier
+#ifndef PIM_DEC_RUNAHEAD
+#define PIM_DEC_RUNAHEAD 256 // (a short run-ahead leaves more history in the ring: fewer back-references go to L2.  Measured on B200, decode GB/s
+                             // corpus / text / mix: 1920: 128.5 / 203.2 / 322.8, 1024: 128.8 / 203.1 / 323.2, 512: 134.1 / 204.5 / 324.8, 256: 141.4 / 202.6 / 321.3,
+                             // 128: 141.8 / 197.7 / 316.2, 64: 138.7 / 191.9 / 306.2)
+#endif
+constexpr uint32_t RUNAHEAD = PIM_DEC_RUNAHEAD; // the window stops fetching when this far ahead of the frontier
 constexpr uint32_t KEEP = 80;            // bytes of a long literal's end that are also put into the ring
 // One refill fetches up to 32 elements of at most 64 bytes on top of the run-ahead: everything between the
 // write frontier and the last fetched byte must fit the ring (measured on B200: a 2 KB ring with 7 or 8 CTAs
