@@ -14,7 +14,7 @@
 //     SM's shared memory fits one more table than six independent CTAs did) keep theirs there;
 //   * as many pairs again keep their table in global memory (L2-resident, ld/st.cg): 0.6x the speed of
 //     a shared-memory pair, and more than one of them per shared-memory pair saturates L2.
-// The input is NOT staged: it is prefetched into L2 and read from there through L1.  The parser warp
+// The input is NOT staged: the parser prefetches it into L2 a few KB ahead of itself and reads it from there through L1.  The parser warp
 // (compress_warp.cuh) fuses the reference's step 1 / step 3 probes into 32-lane passes that resolve
 // several (literal, copy) pairs per shared-memory round trip, the emitter warp turns its per-pass
 // records into bytes.
@@ -126,8 +126,9 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 		c.out = sa.slots + blk * (uint64_t)a.stride;
 		c.n = n;
 
-		for (uint32_t i = ptid * 128u; i < n; i += 64u * 128u) // HBM -> L2 for the whole block, ahead of the parse
-			asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc + i));
+		if (!PIM_PF_AHEAD)
+			for (uint32_t i = ptid * 128u; i < n; i += 64u * 128u) // HBM -> L2 for the whole block, ahead of the parse
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc + i));
 		for (uint32_t i = ptid * 16u; i < 2u * ts; i += 1024u) // get_hash_table, snappy_compress.c:139-146
 			*reinterpret_cast<uint4 *>(tbytes + i) = make_uint4(0, 0, 0, 0);
 		if (ptid == 0) {

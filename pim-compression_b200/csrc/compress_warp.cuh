@@ -50,6 +50,11 @@ constexpr uint32_t CW_MARGIN = 15;       // snappy_compress.c:299
 #define PIM_CW_CHAIN_MAX 30 // (30 = as long as a continuation lane exists; measured on B200, text: 20: 34.4, 24: 37.6, 28: 40.2, 30: 41.2 GB/s)
 #endif
 constexpr int CW_CHAIN_MAX = PIM_CW_CHAIN_MAX; // a new pair is resolved in the same pass if its insert lane is <= this
+#ifndef PIM_PF_AHEAD
+#define PIM_PF_AHEAD 1024 // the parser prefetches the input into L2, 4 KB at a time, when it gets this close to the end of what it has prefetched
+                          // (0: whole block up front, compress_sm100.cu -- with 2,220 blocks in flight that is 72 MB of input parked in L2 next
+                          // to tables and output slots, and part of it was evicted before use: DRAM reads per 256 MiB 529 -> 445 MB, speed +-1 %)
+#endif
 #ifndef PIM_GT_MATCH
 #define PIM_GT_MATCH 1 // global-memory tables: slot sharing inside a pass found with match.any (0: store + read-back, as for shared memory)
 #endif
@@ -463,6 +468,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 	const uint32_t n = c.n;
 	uint32_t emit = 0; // first input byte not yet emitted (next_emit)
 	uint32_t head = 0; // records published so far
+	uint32_t pf = 0;   // input below this position has been prefetched into L2
 
 	if (n >= CW_MARGIN) {
 		const uint32_t limit = n - CW_MARGIN;
@@ -473,6 +479,12 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 			if (has_ic && q >= limit) // :386
 				break;
 			CW_STAT(has_ic ? 0 : 1);
+			if (PIM_PF_AHEAD && pf < n && pf < q + PIM_PF_AHEAD) { // HBM -> L2 a few KB ahead of the parse (32 lines at a time)
+				const uint32_t at = pf + 128u * lane;
+				if (at < n + 24u)
+					wp::prefetch_l2(reinterpret_cast<const uint8_t *>(c.inw) + c.mis + at);
+				pf += 4096u;
+			}
 			// ---- lane layout -----------------------------------------------------------------
 			uint32_t p, stride = 1;
 			if (has_ic) {

@@ -23,6 +23,7 @@ uint32_t reduce_max(uint32_t v);
 void syncwarp();
 void spin_pause();  // inside a wait loop on shared memory written by another warp
 inline void fence_block() {}
+inline void prefetch_l2(const void *) {}
 template <bool GT> inline uint32_t tbl_ld(const uint16_t *t, uint32_t h) { return t[h]; }
 template <bool GT> inline void tbl_st(uint16_t *t, uint32_t h, uint32_t v) { t[h] = (uint16_t)v; }
 inline uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
@@ -53,6 +54,7 @@ __device__ __forceinline__ void syncwarp() { __syncwarp(); }
 #endif
 __device__ __forceinline__ void spin_pause() { __nanosleep(PIM_SPIN_NS); }
 __device__ __forceinline__ void fence_block() { __threadfence_block(); }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // hash-table access: shared memory (GT = false), or global memory served by L2 (GT = true; .cg so that
 // the lanes of the warp always see each other's stores)
 template <bool GT> __device__ __forceinline__ uint32_t tbl_ld(const uint16_t *t, uint32_t h)
