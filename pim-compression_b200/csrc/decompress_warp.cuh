@@ -49,6 +49,9 @@
 #ifndef PIM_DW_BPL
 #define PIM_DW_BPL 8
 #endif
+#ifndef PIM_DW_WSEG
+#define PIM_DW_WSEG 128
+#endif
 #ifndef PIM_DW_NREC
 #define PIM_DW_NREC 128
 #endif
@@ -65,7 +68,10 @@ namespace pimsnappy {
 constexpr uint32_t DW_RB = PIM_DW_RB;                 // bytes of the output ring = bytes of the stage ring
 constexpr uint32_t DW_RMASK = DW_RB - 1;
 constexpr uint32_t DW_CH = DW_RB / 4;                 // compressed bytes per parse chunk (the stage ring holds 4)
-constexpr uint32_t DW_SEG = DW_CH / 32;               // compressed bytes per lane of a parse
+constexpr uint32_t DW_SEG = DW_CH / 32;               // compressed positions per lane when the starts are queued
+constexpr uint32_t DW_WSEG = PIM_DW_WSEG;             // compressed bytes per walking lane of a parse
+constexpr uint32_t DW_NWK = DW_CH / DW_WSEG;          // walking lanes
+constexpr uint32_t DW_NV = DW_WSEG / 32;              // registers of a walker's position set
 constexpr uint32_t DW_BPL = PIM_DW_BPL;               // output bytes per lane of a gather pass
 constexpr uint32_t DW_WB = 32 * DW_BPL;               // output bytes per gather pass
 constexpr uint32_t DW_NREC = PIM_DW_NREC;             // decoded elements kept (ring of 16-byte records)
@@ -75,6 +81,7 @@ constexpr uint32_t DW_BIG = 0x100000u;                // "footprint" of a malfor
 constexpr uint32_t DW_F_FAR = 1, DW_F_NEAR = 2, DW_F_PERIODIC = 4, DW_F_ALL = 7;
 
 static_assert((DW_RB & (DW_RB - 1)) == 0 && DW_SEG >= 16 && DW_SEG <= 32, "ring size: 2048 or 4096");
+static_assert(DW_WSEG % 32 == 0 && DW_WSEG >= 32 && DW_WSEG <= 128 && DW_CH % DW_WSEG == 0, "walker segment: 32, 64 or 128");
 static_assert(DW_BPL == 4 || DW_BPL == 8, "4 or 8 output bytes per lane");
 static_assert((DW_NREC & (DW_NREC - 1)) == 0 && DW_NREC >= 64 && DW_NREC <= 256, "record ring");
 static_assert(DW_QCAP >= DW_NREC + 32 + 64, "queue must hold the record window, a leftover batch and at least some lanes of a chunk");
@@ -197,7 +204,37 @@ PW_FN uint32_t foot_at(const DSm &s, const State &st, uint32_t p)
 	return f;
 }
 
+// bit sets of DW_WSEG positions (one walker's segment) in DW_NV registers; indices are compile-time after unrolling
+PW_FN bool v_test(const uint32_t V[DW_NV], uint32_t r)
+{
+	uint32_t w = 0;
+#pragma unroll
+	for (uint32_t i = 0; i < DW_NV; i++)
+		if ((r >> 5) == i)
+			w = V[i];
+	return (w >> (r & 31u)) & 1u;
+}
+PW_FN void v_set(uint32_t V[DW_NV], uint32_t r)
+{
+#pragma unroll
+	for (uint32_t i = 0; i < DW_NV; i++)
+		if ((r >> 5) == i)
+			V[i] |= 1u << (r & 31u);
+}
+// V = nb | (V without the bits below r)
+PW_FN void v_merge(uint32_t V[DW_NV], const uint32_t nb[DW_NV], uint32_t r)
+{
+#pragma unroll
+	for (uint32_t i = 0; i < DW_NV; i++) {
+		const uint32_t keep = i < (r >> 5) ? 0u : (i == (r >> 5) ? ~((1u << (r & 31u)) - 1u) : 0xFFFFFFFFu);
+		V[i] = nb[i] | (V[i] & keep);
+	}
+}
+
 // Find the element starts of the chunk that holds st.pa, from st.pa on; push them; advance st.pa.
+// The first DW_NWK lanes walk DW_WSEG bytes each (segments long enough that a walk from a guessed start
+// has merged with the true chain before it leaves the segment); every lane then takes the DW_SEG positions
+// of its own and queues the starts among them.
 // A literal with explicit length bytes ends the parse: it is reported in st.bulk / b_src / b_len and
 // st.pa continues after it.
 PW_FN void parse_chunk(const DSm &s, State &st)
@@ -206,42 +243,52 @@ PW_FN void parse_chunk(const DSm &s, State &st)
 	const uint32_t kc = st.pa / DW_CH, cbase = kc * DW_CH;
 	const uint32_t x0 = st.pa - cbase;
 	const uint32_t cend = wp::umin(DW_CH, st.a_end - cbase); // chunk-relative end of the block's data
-	const uint32_t base = DW_SEG * lane;
-	uint32_t lim = wp::umin(base + DW_SEG, cend); // (<= base past the block's end: such a lane is never entered)
-	if (base + DW_SEG <= x0)
-		lim = base; // nothing of mine is at or after the entry
-	const int lastl = (int)((cend - 1) / DW_SEG); // last lane with data
+	const bool walker = (uint32_t)lane < DW_NWK;
+	const uint32_t wbase = walker ? DW_WSEG * lane : DW_CH;
+	uint32_t lim = wp::umin(wbase + DW_WSEG, cend); // (<= wbase past the block's end: such a lane is never entered)
+	if (wbase + DW_WSEG <= x0 || !walker)
+		lim = wbase; // nothing of mine is at or after the entry
+	const int lastl = (int)((cend - 1) / DW_WSEG); // last walker with data
 	DW_STAT(0, 1);
 
 	// speculative walk from the segment start
-	uint32_t V = 0; // bit b: an element of the chain I know starts at base + b
-	uint32_t exitA = base;
+	uint32_t V[DW_NV]; // bit b: an element of the chain I know starts at wbase + b
+#pragma unroll
+	for (uint32_t i = 0; i < DW_NV; i++)
+		V[i] = 0;
+	uint32_t exitA = wbase;
 	{
-		uint32_t p = base;
+		uint32_t p = wbase;
 		while (p < lim) {
-			V |= 1u << (p - base);
+			v_set(V, p - wbase);
 			p += foot_at(s, st, cbase + p);
+			DW_STAT(11, 1);
 		}
 		exitA = p;
 	}
-	// fixed point over the lanes: x = first element start at or after my segment's first byte
-	uint32_t x = wp::umax(base, x0); // (always >= base: lanes before the entry pass the entry along)
-	uint32_t eval_x = base, f_out = 0;
+	// fixed point over the walkers: x = first element start at or after my segment's first byte
+	uint32_t x = wp::umax(wbase, x0); // (always >= wbase: lanes before the entry pass the entry along)
+	uint32_t eval_x = wbase, f_out = 0;
 	for (int it = 0; it < 34; it++) {
 		const bool touched = x < lim;
 		if (touched && x != eval_x) {
 			eval_x = x;
-			const uint32_t r = x - base;
-			if (!((V >> r) & 1u)) { // not on the chain I know: walk until it merges with it
-				uint32_t p = x, nb = 0;
-				while (p < lim && !((V >> (p - base)) & 1u)) {
-					nb |= 1u << (p - base);
+			if (!v_test(V, x - wbase)) { // not on the chain I know: walk until it merges with it
+				uint32_t p = x, nb[DW_NV];
+#pragma unroll
+				for (uint32_t i = 0; i < DW_NV; i++)
+					nb[i] = 0;
+				while (p < lim && !v_test(V, p - wbase)) {
+					v_set(nb, p - wbase);
 					p += foot_at(s, st, cbase + p);
+					DW_STAT(12, 1);
 				}
 				if (p < lim) {
-					V = nb | (V & ~((1u << (p - base)) - 1u));
+					v_merge(V, nb, p - wbase);
 				} else {
-					V = nb;
+#pragma unroll
+					for (uint32_t i = 0; i < DW_NV; i++)
+						V[i] = nb[i];
 					exitA = p;
 				}
 			}
@@ -250,20 +297,49 @@ PW_FN void parse_chunk(const DSm &s, State &st)
 		uint32_t nx = wp::shfl(f_out, lane - 1);
 		if (lane == 0)
 			nx = x0;
-		nx = wp::umax(nx, base);
+		nx = wp::umax(nx, wbase);
 		const bool changed = nx != x && lane <= lastl;
 		x = nx;
 		DW_STAT(1, 1);
 		if (!wp::ballot(changed))
 			break;
 	}
-	const bool touched = x < lim;
-	uint32_t bits = touched ? (V & ~((1u << (x - base)) - 1u)) : 0u;
+	{ // drop what lies before my true entry
+		const bool touched = x < lim;
+		uint32_t none[DW_NV];
+#pragma unroll
+		for (uint32_t i = 0; i < DW_NV; i++)
+			none[i] = 0;
+		if (touched)
+			v_merge(V, none, x - wbase);
+		else {
+#pragma unroll
+			for (uint32_t i = 0; i < DW_NV; i++)
+				V[i] = 0;
+		}
+	}
 	uint32_t next = wp::shfl(f_out, lastl); // chunk-relative start of the first element after the chunk
+	// every lane takes its DW_SEG positions from the walker that owns them
+	const uint32_t base = DW_SEG * lane;
+	uint32_t bits = 0;
+	{
+		const int owner = (int)(base / DW_WSEG);
+		const uint32_t r = base % DW_WSEG;
+#pragma unroll
+		for (uint32_t i = 0; i < DW_NV; i++) {
+			const uint32_t t = wp::shfl(V[i], owner);
+			if ((r >> 5) == i)
+				bits = t;
+		}
+		bits >>= (r & 31u);
+		if (DW_SEG < 32)
+			bits &= (1u << DW_SEG) - 1u;
+	}
 
 	// a literal with explicit length bytes: the last element of its segment (its footprint is > 62 bytes)
 	uint32_t b_a = 0, b_nb = 0, b_len = 0;
 	bool isbulk = false;
+	const uint32_t first_pos = bits ? base + (uint32_t)wp::ffs32(bits) - 1u : 0xFFFFFFFFu; // my first element start
 	if (bits) {
 		const uint32_t hb = 31u - (uint32_t)wp::clz32(bits);
 		const uint32_t p = cbase + base + hb;
@@ -297,7 +373,9 @@ PW_FN void parse_chunk(const DSm &s, State &st)
 		total = wp::shfl(incl, m ? m - 1 : 0);
 		if (!m)
 			total = 0;
-		next = wp::shfl(x, m);
+		const uint32_t fn = wp::reduce_min(lane >= m ? first_pos : 0xFFFFFFFFu); // first start that was not queued
+		if (fn != 0xFFFFFFFFu)
+			next = fn;
 		if (lb >= m)
 			lb = 32;
 	} else {
