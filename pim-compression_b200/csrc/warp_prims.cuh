@@ -1,4 +1,4 @@
-// Warp primitives used by the per-warp compressor (compress_warp.cuh) and decoder (decompress_warp.cuh).
+// Warp primitives used by the per-warp compressor (compress_warp.cuh).
 //
 // Device build: thin wrappers over the sm_100a intrinsics.
 // Host build with PIM_WARP_EMU: the same names run on a lock-step emulator (32 cooperative
@@ -20,7 +20,6 @@ uint32_t ballot(bool pred);
 uint32_t shfl(uint32_t v, int src_lane);
 uint32_t match_any(uint32_t v);
 uint32_t reduce_max(uint32_t v);
-uint32_t reduce_min(uint32_t v);
 void syncwarp();
 void spin_pause();  // inside a wait loop on shared memory written by another warp
 inline void fence_block() {}
@@ -36,15 +35,6 @@ inline int ffs32(uint32_t v) { return __builtin_ffs((int)v); }
 inline int clz32(uint32_t v) { return v ? __builtin_clz(v) : 32; }
 inline int popc32(uint32_t v) { return __builtin_popcount(v); }
 inline uint32_t umin(uint32_t a, uint32_t b) { return a < b ? a : b; }
-inline uint32_t umax(uint32_t a, uint32_t b) { return a > b ? a : b; }
-// global memory / async staging as the decoder (decompress_warp.cuh) uses them
-inline uint32_t ldg8(const uint8_t *p) { return *p; }
-inline uint32_t ldg32(const uint32_t *p) { return *p; }
-inline uint32_t ld8_l2(const uint8_t *p) { return *p; }
-inline void st_global_u8(uint8_t *p, uint32_t v) { *p = (uint8_t)v; }
-inline void cp16(void *smem_dst, const void *gsrc) { __builtin_memcpy(smem_dst, gsrc, 16); }
-inline void cp_commit() {}
-inline void cp_wait_all() {}
 } // namespace wp
 } // namespace pimsnappy
 
@@ -87,25 +77,6 @@ __device__ __forceinline__ int ffs32(uint32_t v) { return __ffs((int)v); }
 __device__ __forceinline__ int clz32(uint32_t v) { return __clz((int)v); }
 __device__ __forceinline__ int popc32(uint32_t v) { return __popc(v); }
 __device__ __forceinline__ uint32_t umin(uint32_t a, uint32_t b) { return min(a, b); }
-__device__ __forceinline__ uint32_t umax(uint32_t a, uint32_t b) { return max(a, b); }
-__device__ __forceinline__ uint32_t reduce_min(uint32_t v) { return __reduce_min_sync(0xFFFFFFFFu, v); }
-__device__ __forceinline__ uint32_t ldg8(const uint8_t *p) { return __ldg(p); }
-__device__ __forceinline__ uint32_t ldg32(const uint32_t *p) { return __ldg(p); }
-// a byte this warp stored to global memory earlier (read at L2; ordered after the store by __syncwarp)
-__device__ __forceinline__ uint32_t ld8_l2(const uint8_t *p)
-{
-	uint32_t v;
-	asm volatile("ld.global.cg.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-	return v;
-}
-__device__ __forceinline__ void st_global_u8(uint8_t *p, uint32_t v) { *p = (uint8_t)v; }
-__device__ __forceinline__ void cp16(void *smem_dst, const void *gsrc)
-{
-	const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
-	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 } // namespace wp
 } // namespace pimsnappy
 

@@ -1,4 +1,4 @@
-// Lock-step warp emulator for the per-warp compressor and decoder (test infrastructure, CPU only).
+// Lock-step warp emulator for the per-warp compressor (test infrastructure, CPU only).
 //
 // Compiles pim-compression_b200/csrc/compress_warp.cuh -- the very source the CUDA kernel
 // includes -- with PIM_WARP_EMU, and runs its 32 lanes as 32 cooperative contexts that meet
@@ -17,22 +17,11 @@
 
 #define PIM_WARP_EMU_STATS
 #include "../../pim-compression_b200/csrc/compress_warp.cuh"
-#include "../../pim-compression_b200/csrc/decompress_warp.cuh"
 
 namespace pimsnappy {
-unsigned long dw_stats[16]; // decoder: 0 parses, 1 fixed-point iterations, 2 batches, 3 elements, 4 passes, 5 bytes of passes, 6 search groups,
-                            // 7 passes with slow bytes, 8 fix-up rounds, 9 bulk literals, 10 forced drains
 unsigned long cw_stats[8]; // 0 ic passes, 1 probe passes, 2 pairs, 3 redone pairs, 4 long matches, 5 serial re-resolves, 6 passes with shared slots
 }
 extern "C" void emu_set_order(int order);
-extern "C" void emu_dw_stats(unsigned long out[16], int reset)
-{
-	for (int i = 0; i < 16; i++) {
-		out[i] = pimsnappy::dw_stats[i];
-		if (reset)
-			pimsnappy::dw_stats[i] = 0;
-	}
-}
 extern "C" void emu_stats(unsigned long out[8], int reset)
 {
 	for (int i = 0; i < 8; i++) {
@@ -182,15 +171,6 @@ uint32_t reduce_max(uint32_t v)
 		return m;
 	});
 }
-uint32_t reduce_min(uint32_t v)
-{
-	return exchange(6, v, [] {
-		uint32_t m = 0xFFFFFFFFu;
-		for (int l = 0; l < NL; l++)
-			m = g_slot[wbase() + l] < m ? g_slot[wbase() + l] : m;
-		return m;
-	});
-}
 void syncwarp()
 {
 	exchange(4, 0, [] { return 0u; });
@@ -269,107 +249,4 @@ extern "C" uint64_t emu_compress(const uint8_t *in, uint64_t len, uint32_t block
 		o += j.result;
 	}
 	return o;
-}
-
-// ---------------------------------------------------------------------------------------------
-// Decoder (decompress_warp.cuh): one emulated warp per block.
-// ---------------------------------------------------------------------------------------------
-namespace {
-
-struct DJob {
-	pimsnappy::DSm sm;
-	pimsnappy::DBlk blk;
-	int ok;
-};
-
-void dbody(void *arg)
-{
-	DJob *j = static_cast<DJob *>(arg);
-	if (g_cur >= NL)
-		return; // one warp decodes
-	const bool ok = pimsnappy::decode_block_warp(j->sm, j->blk);
-	if (pimsnappy::wp::lane() == 0)
-		j->ok = ok ? 1 : 0;
-}
-
-size_t get_varint(const uint8_t *p, size_t n, uint32_t *v) // snappy_decompress.c:23-37
-{
-	uint32_t r = 0;
-	for (size_t k = 0; k < 5 && k < n; k++) {
-		r |= (uint32_t)(p[k] & 127) << (7 * k);
-		if (!(p[k] & 128)) {
-			*v = r;
-			return k + 1;
-		}
-	}
-	return 0;
-}
-
-} // namespace
-
-extern "C" uint32_t emu_dw_config(int which)
-{
-	using namespace pimsnappy;
-	return which == 0 ? DW_RB : (which == 1 ? DW_BPL : DW_NREC);
-}
-
-// Decode the file image in[0..len) (header varints + blocks) into out (capacity cap).  Returns the decoded
-// length, or -1 (malformed header / block structure), -2 (a block failed to decode), -3 (bytes outside the output
-// were written).  `shift` (0..15) moves the compressed bytes and the output to other 16-byte phases, as
-// sub-buffers on the device have them.
-extern "C" long emu_decompress(const uint8_t *in, uint64_t len, uint8_t *out, uint64_t cap, int shift)
-{
-	using namespace pimsnappy;
-	uint32_t dlen = 0, bs = 0;
-	size_t o = get_varint(in, len, &dlen);
-	if (!o)
-		return -1;
-	const size_t o2 = get_varint(in + o, len - o, &bs);
-	if (!o2 || bs == 0 || dlen > cap)
-		return -1;
-	o += o2;
-	// private copies with guard bytes, at the requested phase
-	std::vector<uint8_t> cbuf(len + 64 + 32, 0xEE), obuf((size_t)dlen + 64 + 32, 0xDD);
-	uint8_t *cb = cbuf.data() + 32 - (reinterpret_cast<uintptr_t>(cbuf.data()) & 15) + (shift & 15);
-	uint8_t *ob = obuf.data() + 32 - (reinterpret_cast<uintptr_t>(obuf.data()) & 15) + ((shift * 7) & 15);
-	memcpy(cb, in, len);
-	constexpr uint32_t SMB = 2 * DW_RB + DW_SMALL_BYTES + 256;
-	static uint8_t *smem = nullptr;
-	if (!smem)
-		smem = static_cast<uint8_t *>(aligned_alloc(4096, (SMB + 4095) & ~4095u));
-	for (uint32_t t = 0; t < 256; t++)
-		smem[2 * DW_RB + DW_SMALL_BYTES + t] = (uint8_t)dw_lut_foot(t);
-	uint64_t at = 0;
-	while (at < dlen) {
-		if (o + 4 > len)
-			return -1;
-		const uint32_t csize = (uint32_t)cb[o] | (uint32_t)cb[o + 1] << 8 | (uint32_t)cb[o + 2] << 16 | (uint32_t)cb[o + 3] << 24;
-		if (csize == 0 || o + 4 + (uint64_t)csize > len)
-			return -1;
-		DJob j;
-		j.sm.sm = smem;
-		j.sm.ring = 0;
-		j.sm.stg = DW_RB;
-		j.sm.q = 2 * DW_RB;
-		j.sm.rec = 2 * DW_RB + 2 * DW_QCAP;
-		j.sm.lut = 2 * DW_RB + DW_SMALL_BYTES;
-		memset(smem, 0xA7, 2 * DW_RB + DW_SMALL_BYTES); // stale bytes of a previous block must not matter
-		j.blk.gcomp = cb + o + 4;
-		j.blk.csize = csize;
-		j.blk.gdst = ob + at;
-		j.blk.out_size = (uint32_t)((dlen - at < bs) ? dlen - at : bs);
-		j.ok = 0;
-		run_warp(dbody, &j);
-		if (!j.ok)
-			return -2;
-		o += 4 + csize;
-		at += j.blk.out_size;
-	}
-	if (o != len)
-		return -1;
-	for (int i = 1; i <= 16; i++)
-		if (ob[-i] != 0xDD || ob[dlen + i - 1] != 0xDD)
-			return -3;
-	memcpy(out, ob, dlen);
-	return (long)dlen;
 }
