@@ -13,16 +13,11 @@
 //     16-byte stores.  Back-references (write_copy_host, snappy_decompress.c:164-184) that reach
 //     back further than the ring are read from HBM/L2 (ld.global.cg), which this warp wrote
 //     itself a while ago;
-//   * the serial TAG CHAIN of the block (an element's length says where the next tag is) is found ONCE PER
-//     BLOCK, before any byte moves: the block's compressed bytes are cut into 32 equal pieces, every lane
-//     walks its piece from the piece's first byte (a guess; the walks are serial but all 32 lanes are busy),
-//     marking what it visits in a bitmap (one bit per compressed byte, in global memory / L2).  A walk from
-//     a wrong start falls onto the true chain within a few elements, so once lane l-1's exit is known lane l
-//     only re-walks from its true entry until it meets its own marks.  (Walking 32-byte segments of each 1 KB
-//     chunk instead -- round 1 -- merged too rarely inside literal payloads: 7 fixed-point iterations per
-//     chunk, a quarter of all instructions);
-//   * the compressed bytes are staged in 1 KB chunks (cp.async, double-buffered); the element starts of a
-//     chunk are read from the bitmap, one 32-bit word per lane;
+//   * the compressed bytes are staged in 1 KB chunks (cp.async, double-buffered).  The serial tag
+//     chain of a chunk (an element's length says where the next tag is) is found by 32 lanes
+//     WALKING 32-byte segments speculatively from their segment starts, then iterating
+//     x[s+1] = exit_s(x[s]) to the fixed point: a lane whose true entry lies on the chain it
+//     already walked is done, otherwise it re-walks until it merges with that chain;
 //   * elements are executed through a sliding window of 32 in-flight elements, one per lane:
 //     an element runs as soon as every output byte below its source end is complete, finished
 //     lanes are refilled, so a copy that depends on its neighbours delays only itself.
@@ -83,13 +78,6 @@ constexpr uint32_t SM_WARP0 = 512;
 constexpr uint32_t SMEM_BYTES = SM_WARP0 + WARPS * WS_BYTES;
 
 constexpr uint32_t BIG_FOOT = 0x100000u;
-// per-warp scratch in global memory (pre-parse): the bitmap of element starts, then the first element start at or
-// after every chunk boundary
-constexpr uint32_t PP_BM_WORDS = 2560;             // covers 81,920 compressed bytes (a 64 KiB block is at most 76,470)
-constexpr uint32_t PP_ENT = 96;                    // chunk boundaries
-constexpr uint32_t PP_WORDS = PP_BM_WORDS + PP_ENT;
-
-__device__ __forceinline__ void stcg32(uint32_t *p, uint32_t v) { asm volatile("st.global.cg.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
 
 __device__ __forceinline__ uint32_t ldcg32(const uint32_t *p)
 {
@@ -148,7 +136,6 @@ struct Dec {
 	uint32_t fw;          // 16-byte words (of gdst - g15) flushed so far
 	uint32_t ring_lo;     // output bytes below this are not in the ring (they went to HBM directly)
 	bool runs;            // (warp-uniform) some pending element continues a run of copies
-	uint32_t *pp;         // this warp's pre-parse scratch (PP_WORDS words of global memory)
 };
 
 __device__ __forceinline__ uint32_t ring_off(const Dec &d, uint32_t p) { return (p + d.g15) & RMASK; }
@@ -180,182 +167,70 @@ __device__ __forceinline__ void flush_words(Dec &d, uint32_t upto)
 // Returns the number of elements; fills WS_REC / WS_SEGBASE; *chunk_out = bytes they produce,
 // *next_cp = compressed position of the first element after the chunk.
 // ---------------------------------------------------------------------------
-// ---------------------------------------------------------------------------
-// Pre-parse: the block's tag chain as a bitmap (bit p of d.pp: an element starts at compressed position p) and,
-// for every chunk boundary k * CHUNK, the first element start at or after it (d.pp[PP_BM_WORDS + k]).
-// Returns false if the chain is malformed.
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t foot_global(const Dec &d, uint32_t p)
+__device__ __forceinline__ uint32_t foot_at(const Dec &d, uint32_t stage, uint32_t p, uint32_t cs)
 {
-	const uint32_t tag = __ldg(d.gcomp + p);
-	uint32_t f = d.sm[SM_LUT_FOOT + tag];
-	if (f == 0) { // literal with 1..4 length bytes
-		const uint32_t nb = (tag >> 2) - 59;
-		if (p + 1 + nb > d.csize)
-			return BIG_FOOT;
-		uint32_t lm1 = 0;
-		for (uint32_t i = 0; i < nb; i++)
-			lm1 |= (uint32_t)__ldg(d.gcomp + p + 1 + i) << (8 * i);
-		if (lm1 >= 65536u)
-			return BIG_FOOT;
-		f = 2 + nb + lm1;
+	uint32_t f = d.sm[SM_LUT_FOOT + d.ws[stage + p]];
+	if (f == 0) {
+		uint32_t len;
+		f = long_literal(d.ws, stage + p, cs + p, d.csize, &len);
 	}
 	return f;
 }
 
-// Walk from p to the end of my piece, writing the words of the bitmap as they are completed.  `stop_at_mark`: stop at
-// the first position that is already marked (the chain I walked before), keeping the marks from there on.
-// Returns where the walk stopped (>= lim: left the piece).  Words before p's word are not touched.
-__device__ __forceinline__ uint32_t walk_piece(const Dec &d, uint32_t p, uint32_t lim, bool stop_at_mark)
-{
-	uint32_t wi = p >> 5;
-	uint32_t old = stop_at_mark ? ldcg32(d.pp + wi) : 0u;
-	uint32_t acc = 0; // new marks of word wi (what the word held below the entry is dropped)
-	while (p < lim) {
-		const uint32_t w = p >> 5;
-		if (w != wi) { // finished word wi: the marks I made (everything I knew before was off the chain)
-			stcg32(d.pp + wi, acc);
-			for (uint32_t z = wi + 1; z < w; z++)
-				stcg32(d.pp + z, 0u);
-			wi = w;
-			acc = 0;
-			old = stop_at_mark ? ldcg32(d.pp + wi) : 0u;
-		}
-		const uint32_t bit = 1u << (p & 31u);
-		if (stop_at_mark && (old & bit)) { // met the chain I know: its marks from here on are right
-			stcg32(d.pp + wi, acc | (old & ~(bit - 1u)));
-			return p;
-		}
-		acc |= bit;
-		p += foot_global(d, p);
-	}
-	// left the piece: the rest of my words (up to lim) hold nothing
-	stcg32(d.pp + wi, acc);
-	for (uint32_t z = wi + 1; z < (lim + 31u) >> 5; z++)
-		stcg32(d.pp + z, 0u);
-	return p;
-}
-
-__device__ __forceinline__ bool preparse_block(const Dec &d)
+__device__ __forceinline__ uint32_t parse_chunk(Dec &d, uint32_t stage, uint32_t cs, uint32_t x0, uint32_t *chunk_out, uint32_t *next_cp)
 {
 	const int lane = d.lane;
-	{ // a block that is one literal (incompressible data): nothing to walk
-		const uint32_t tag0 = __ldg(d.gcomp);
-		if ((tag0 & 3u) == 0u && (tag0 >> 2) >= 60u && foot_global(d, 0) == d.csize) {
-			const uint32_t nwords = (d.csize + 31u) >> 5;
-			if ((uint32_t)lane < nwords)
-				stcg32(d.pp + lane, lane == 0 ? 1u : 0u);
-			for (uint32_t k = lane; k <= d.csize / CHUNK + 1 && k < PP_ENT; k += 32)
-				stcg32(d.pp + PP_BM_WORDS + k, k == 0 ? 0u : d.csize);
-			__syncwarp();
-			return true;
-		}
-	}
-	const uint32_t piece = max(64u, (((d.csize + 31u) / 32u) + 31u) & ~31u); // bytes per lane, a multiple of 32
-	const uint32_t base = min(piece * lane, d.csize & ~31u);
-	const uint32_t lim = min(piece * (lane + 1), d.csize);
-	const bool mine = piece * lane < d.csize; // my piece holds data
-	const int lastl = (int)((d.csize - 1) / piece);
-	// speculative walk from the piece's first byte
+	const uint32_t csz = d.csize - cs;             // bytes from the chunk start to the block's end
+	const uint32_t base = SEGB * lane;
+	const uint32_t lim = min(base + SEGB, csz);    // my segment is [base, lim)
+
+	// ---- speculative walk from the segment start ------------------------------------------
+	uint32_t V = 0;      // bit b: an element of my chain starts at base + b
 	uint32_t exitA = base;
-	if (mine)
-		exitA = walk_piece(d, base, lim, false);
-	__syncwarp();
-	// fixed point: x = first element start at or after my piece's first byte (true for lane 0)
-	uint32_t x = lane == 0 ? 0u : base;
-	uint32_t eval_x = base;
+	{
+		uint32_t p = base;
+		while (p < lim) {
+			V |= 1u << (p - base);
+			p += foot_at(d, stage, p, cs);
+		}
+		exitA = p;
+	}
+	// ---- fixed point over the lanes --------------------------------------------------------
+	uint32_t x = lane == 0 ? x0 : base; // first element start at or after my segment
+	uint32_t eval_x = base, r = 0;
 	uint32_t f_out = 0;
 	for (int it = 0; it < 34; it++) {
-		const bool touched = mine && x < lim;
+		const bool touched = x < lim;  // (x >= base always)
 		if (touched && x != eval_x) {
 			eval_x = x;
-			// nothing before the entry is an element
-			for (uint32_t z = base >> 5; z < (x >> 5); z++)
-				stcg32(d.pp + z, 0u);
-			const uint32_t xw = ldcg32(d.pp + (x >> 5));
-			if ((xw >> (x & 31u)) & 1u) {
-				stcg32(d.pp + (x >> 5), xw & ~((1u << (x & 31u)) - 1u)); // on the chain I walked: keep it from x on
-			} else {
-				const uint32_t stop = walk_piece(d, x, lim, true);
-				if (stop >= lim)
-					exitA = stop;
+			r = x - base;
+			if (!((V >> r) & 1u)) { // not on the chain I know: walk until it merges with it
+				uint32_t p = x, nb = 0;
+				while (p < lim && !((V >> (p - base)) & 1u)) {
+					nb |= 1u << (p - base);
+					p += foot_at(d, stage, p, cs);
+				}
+				if (p < lim) {
+					V = nb | (V & ~((1u << (p - base)) - 1u));
+				} else {
+					V = nb;
+					exitA = p;
+				}
 			}
 		}
 		f_out = touched ? exitA : x;
 		uint32_t nx = __shfl_up_sync(FULL, f_out, 1);
 		if (lane == 0)
-			nx = 0;
-		nx = max(nx, base);
-		const bool changed = nx != x && lane <= lastl;
+			nx = x0;
+		const bool changed = nx != x;
 		x = nx;
 		if (!__any_sync(FULL, changed))
 			break;
 	}
-	// a lane whose piece the chain jumps over holds no element
-	if (mine && !(x < lim)) {
-		for (uint32_t z = base >> 5; z < (lim + 31u) >> 5; z++)
-			stcg32(d.pp + z, 0u);
-	}
-	const uint32_t end = __shfl_sync(FULL, f_out, lastl);
-	__syncwarp();
-	// first element start at or after every chunk boundary: per chunk the first mark (32 words, one per lane), then a
-	// suffix minimum over the chunks
-	const uint32_t nwords = (d.csize + 31u) >> 5;
-	const uint32_t nch = d.csize / CHUNK + 1; // chunks that hold data (the last may be empty), boundaries 0..nch
-	uint32_t carry = d.csize;
-	for (int r = (int)((nch + 32u) / 32u) - 1; r >= 0; r--) { // (boundaries 0..nch inclusive)
-		uint32_t mine_first = d.csize; // first mark of chunk 32 r + lane
-		for (uint32_t j = 0; j < 32; j++) {
-			const uint32_t k = 32u * r + j;
-			if (k >= nch)
-				break;
-			const uint32_t w = (k * CHUNK >> 5) + lane;
-			const uint32_t v = w < nwords ? ldcg32(d.pp + w) : 0u;
-			const uint32_t nz = __ballot_sync(FULL, v != 0u);
-			if (nz) {
-				const int l = __ffs(nz) - 1;
-				const uint32_t vv = __shfl_sync(FULL, v, l);
-				if ((uint32_t)lane == j)
-					mine_first = k * CHUNK + 32u * l + (uint32_t)__ffs(vv) - 1u;
-			}
-		}
-		// suffix minimum inside the round, then with the rounds above
-		uint32_t m = mine_first;
-#pragma unroll
-		for (int dd = 1; dd < 32; dd <<= 1) {
-			const uint32_t t = __shfl_down_sync(FULL, m, dd);
-			if (lane + dd < 32)
-				m = min(m, t);
-		}
-		m = min(m, carry);
-		const uint32_t k = 32u * r + lane;
-		if (k <= nch && k < PP_ENT)
-			stcg32(d.pp + PP_BM_WORDS + k, m);
-		carry = __shfl_sync(FULL, m, 0);
-	}
-	__syncwarp();
-	return end == d.csize; // the last element must end exactly at the block's end
-}
-
-// ---------------------------------------------------------------------------
-// Parse one staged chunk: the element starts come from the pre-parse.  Positions are relative to the chunk.
-//   stage : shared-memory offset (in d.ws) of the chunk's first byte
-//   cs    : compressed position of the chunk's first byte;  x0: entry (first element start)
-// Returns the number of elements; fills WS_REC / WS_SEGBASE; *chunk_out = bytes they produce,
-// *next_cp = compressed position of the first element after the chunk.
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t parse_chunk(Dec &d, uint32_t stage, uint32_t cs, uint32_t x0, uint32_t *chunk_out, uint32_t *next_cp)
-{
-	const int lane = d.lane;
-	const uint32_t base = SEGB * lane;
-	uint32_t bits = 0;
-	if (cs + base < d.csize)
-		bits = ldcg32(d.pp + ((cs + base) >> 5));
-	if (x0 >= base + SEGB)
-		bits = 0;
-	else if (x0 > base)
-		bits &= ~((1u << (x0 - base)) - 1u);
-	*next_cp = ldcg32(d.pp + PP_BM_WORDS + cs / CHUNK + 1);
+	const bool touched = x < lim;
+	uint32_t bits = touched ? (V & ~((1u << r) - 1u)) : 0u;
+	const uint32_t nx_all = __shfl_sync(FULL, f_out, 31);
+	*next_cp = nx_all >= BIG_FOOT ? 0xFFFFFFFFu : cs + nx_all;
 
 	// ---- records: compressed position + output offset inside my segment ---------------------
 	const uint32_t cnt = __popc(bits);
@@ -655,11 +530,6 @@ __device__ __forceinline__ void decode_block(Dec &d)
 	};
 	uint32_t staged_cs = 0; // chunk in flight / present in `buf`
 	stage_chunk(0, 0);
-	if (d.csize > PP_BM_WORDS * 32u || !preparse_block(d)) { // (while the first chunk is on its way)
-		d.err = true;
-		cp_async_wait<0>();
-		return;
-	}
 
 	for (;;) {
 		const uint32_t cs = (cp / CHUNK) * CHUNK;
@@ -769,9 +639,9 @@ __device__ __forceinline__ void decode_block(Dec &d)
 }
 
 // ---------------------------------------------------------------------------
-// Kernel: persistent CTAs of WARPS independent warps; warp g of the grid decodes blocks
-// g, g + total_warps, ... of the concatenation of the batch's streams' blocks (one launch decodes up to
-// DEC_MAX_BATCH streams, pim_snappy_decompress_batch_device, so that no SM idles between streams).
+// Kernel: persistent CTAs of WARPS independent warps; every warp pulls the next block of the concatenation of
+// the batch's streams' blocks from a counter (one launch decodes up to DEC_MAX_BATCH streams,
+// pim_snappy_decompress_batch_device, so that no SM idles between streams).
 // ---------------------------------------------------------------------------
 constexpr uint32_t DEC_MAX_BATCH = 32;
 struct DecStream {
@@ -788,7 +658,6 @@ struct DecArgs {
 	uint64_t nblocks;   // of the whole batch
 	uint32_t *status;   // one word per stream
 	unsigned long long *counter; // next block of the batch (zero at launch)
-	uint32_t *scratch;  // PP_WORDS words per warp of the grid
 };
 
 __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_kernel(const __grid_constant__ DecArgs a)
@@ -808,7 +677,6 @@ __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_ke
 	d.sm = sm;
 	d.ws = sm + SM_WARP0 + warp * WS_BYTES;
 	d.lane = lane;
-	d.pp = a.scratch + ((size_t)blockIdx.x * WARPS + warp) * PP_WORDS;
 	// every warp pulls the next block of the batch (the reference hands each tasklet a fixed contiguous run,
 	// dpu-decompress/dpu_task.c:42-77; with a queue a warp that drew slow blocks does not set the tail)
 	for (;;) {
@@ -847,16 +715,12 @@ __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_ke
 	}
 }
 
-// Per-device resources of the decoder: block counters (one 8-byte slot per launch, taken round robin and zeroed on the
-// launch's stream right before the kernel; POOL launches would have to be in flight for a clash) and the pre-parse
-// scratch of every resident warp.
+// Block counters: one 8-byte slot per launch, taken round robin from a per-device pool and zeroed on the launch's
+// stream right before the kernel (POOL launches would have to be in flight for a clash).
 constexpr int POOL = 4096;
-constexpr int SCRATCH_SLOTS = 2; // launches that may run at the same time (others wait for a slot, on the device)
 struct DecDevice {
 	unsigned long long *counters = nullptr;
-	uint32_t *scratch = nullptr;    // SCRATCH_SLOTS x (PP_WORDS words per warp of a full grid)
-	cudaEvent_t slot_done[SCRATCH_SLOTS] = {};
-	unsigned next = 0, next_slot = 0;
+	unsigned next = 0;
 	int max_ctas = 0;
 };
 std::mutex g_dec_mu;
@@ -888,7 +752,6 @@ extern "C" snappy_status pim_snappy_decompress_batch_device(int n_streams, const
 	if (dev >= 64 || launches > POOL)
 		return SNAPPY_INVALID_INPUT;
 	unsigned long long *counters = nullptr;
-	uint32_t *scratch = nullptr;
 	int max_ctas = 0;
 	{
 		std::lock_guard<std::mutex> lk(g_dec_mu);
@@ -900,16 +763,12 @@ extern "C" snappy_status pim_snappy_decompress_batch_device(int n_streams, const
 			PIM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, snappy_decompress_kernel, 32 * WARPS, SMEM_BYTES));
 			PIM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 			dd.max_ctas = per_sm * sms > 0 ? per_sm * sms : 1;
-			PIM_CUDA_TRY(cudaMalloc(&dd.scratch, sizeof(uint32_t) * PP_WORDS * (size_t)dd.max_ctas * WARPS * SCRATCH_SLOTS));
-			for (int i = 0; i < SCRATCH_SLOTS; i++)
-				PIM_CUDA_TRY(cudaEventCreateWithFlags(&dd.slot_done[i], cudaEventDisableTiming));
 			PIM_CUDA_TRY(cudaMalloc(&dd.counters, sizeof(unsigned long long) * POOL));
 		}
 		if (dd.next + launches > (unsigned)POOL)
 			dd.next = 0;
 		counters = dd.counters + dd.next;
 		dd.next += launches;
-		scratch = dd.scratch;
 		max_ctas = dd.max_ctas;
 	}
 	int launch_i = 0;
@@ -936,17 +795,9 @@ extern "C" snappy_status pim_snappy_decompress_batch_device(int n_streams, const
 		PIM_CUDA_TRY(cudaMemsetAsync(da.counter, 0, sizeof(unsigned long long), st));
 		const uint64_t want = (total + WARPS - 1) / WARPS;
 		const unsigned grid = (unsigned)(want < (uint64_t)max_ctas ? want : (uint64_t)max_ctas);
-		{
-			std::lock_guard<std::mutex> lk(g_dec_mu);
-			DecDevice &dd = g_dec[dev];
-			const unsigned slot = dd.next_slot++ % SCRATCH_SLOTS;
-			da.scratch = scratch + (size_t)slot * PP_WORDS * (size_t)max_ctas * WARPS;
-			PIM_CUDA_TRY(cudaStreamWaitEvent(st, dd.slot_done[slot], 0)); // (a never-recorded event does not block)
-			prof_begin(3, st);
-			snappy_decompress_kernel<<<grid, 32 * WARPS, SMEM_BYTES, st>>>(da);
-			prof_end(3, st);
-			PIM_CUDA_TRY(cudaEventRecord(dd.slot_done[slot], st));
-		}
+		prof_begin(3, st);
+		snappy_decompress_kernel<<<grid, 32 * WARPS, SMEM_BYTES, st>>>(da);
+		prof_end(3, st);
 		note_launch();
 	}
 	PIM_CUDA_TRY(cudaGetLastError());
