@@ -77,8 +77,10 @@ snappy_status setup_decompression(struct host_buffer_context *input, struct host
  * output->buffer[0 .. output->length) holds the complete file image, byte
  * identical to the reference's snappy_compress_host(); runtime fields filled
  * (pre is accumulated with +=, as in the reference :528).  Unlike the DPU
- * path (:626-627,697-703) it does not fwrite() the file itself -- the CLI
- * writes output->buffer. */
+ * path (:626-627,697-703) it does not fwrite() the file itself unless
+ * pim_snappy_set_write_file(1) was called -- the CLI writes output->buffer
+ * (see INTEGRATION.md).  The host entry points are serialised internally:
+ * they may be called from several threads, one runs at a time. */
 snappy_status snappy_compress_dpu(struct host_buffer_context *input, struct host_buffer_context *output,
                                   uint32_t block_size, struct program_runtime *runtime);
 
@@ -88,7 +90,14 @@ snappy_status snappy_compress_dpu(struct host_buffer_context *input, struct host
 snappy_status snappy_decompress_dpu(struct host_buffer_context *input, struct host_buffer_context *output,
                                     struct program_runtime *runtime);
 
-/* Preferred names for the same two functions. */
+/* The reference's DPU compressor writes output->file_name itself (snappy_compress.c:626-627,697-703) and its
+ * main() skips write_output_host for that case (dpu_snappy.c:209).  With enable != 0 (or $PIM_SNAPPY_WRITE_FILE=1
+ * in the environment) snappy_compress_dpu() does the same after filling output->buffer, so the reference's
+ * unmodified main() links against this library and still produces the file.  Default: off (the CLI shipped
+ * here writes the buffer, like the host path). */
+void pim_snappy_set_write_file(int enable);
+
+/* Preferred names for the same two functions (they never write files). */
 snappy_status snappy_compress_gpu(struct host_buffer_context *input, struct host_buffer_context *output,
                                   uint32_t block_size, struct program_runtime *runtime);
 snappy_status snappy_decompress_gpu(struct host_buffer_context *input, struct host_buffer_context *output,

@@ -54,10 +54,12 @@ inline void plan_pairs(uint32_t block_size, uint32_t smem_budget, uint32_t *n_sm
 	ns = std::max(1u, std::min(ns, MAX_PAIRS));
 	const uint32_t ctl_room = (smem_budget - 64u - ns * tbytes) / PAIR_CTL_BYTES; // pairs the rest has control blocks for
 	uint32_t ng = std::min(std::min(MAX_PAIRS - ns, MAX_GT), std::min(ns + 1u, ctl_room > ns ? ctl_room - ns : 0u));
-	if (const char *e = getenv("PIM_SNAPPY_NSM")) // development aids
-		ns = std::max(1u, std::min(ns, (uint32_t)atoi(e)));
-	if (const char *e = getenv("PIM_SNAPPY_NGT"))
-		ng = std::min(ng, (uint32_t)atoi(e));
+	static const int env_nsm = [] { const char *e = getenv("PIM_SNAPPY_NSM"); return e ? atoi(e) : -1; }(); // development aids, read once
+	static const int env_ngt = [] { const char *e = getenv("PIM_SNAPPY_NGT"); return e ? atoi(e) : -1; }();
+	if (env_nsm >= 0)
+		ns = std::max(1u, std::min(ns, (uint32_t)env_nsm));
+	if (env_ngt >= 0)
+		ng = std::min(ng, (uint32_t)env_ngt);
 	*n_sm = ns;
 	*n_gt = ng;
 }

@@ -33,7 +33,8 @@ static std::atomic<int> g_prof{0};
 static std::mutex g_prof_mu;
 struct ProfSpan { int which; cudaEvent_t a, b; };
 static std::vector<ProfSpan> g_spans;       // completed begin/end pairs awaiting a read
-static cudaEvent_t g_open[4] = {nullptr, nullptr, nullptr, nullptr};
+struct ProfOpen { int which; cudaStream_t st; cudaEvent_t a; };
+static std::vector<ProfOpen> g_open;        // begun, not yet ended: keyed by (kernel kind, stream)
 
 void prof_begin(int which, cudaStream_t st)
 {
@@ -44,7 +45,7 @@ void prof_begin(int which, cudaStream_t st)
 	if (cudaEventCreate(&e) != cudaSuccess)
 		return;
 	cudaEventRecord(e, st);
-	g_open[which] = e;
+	g_open.push_back({which, st, e});
 }
 
 void prof_end(int which, cudaStream_t st)
@@ -52,14 +53,17 @@ void prof_end(int which, cudaStream_t st)
 	if (!g_prof.load(std::memory_order_relaxed))
 		return;
 	std::lock_guard<std::mutex> lk(g_prof_mu);
-	if (!g_open[which])
+	for (size_t i = g_open.size(); i-- > 0;) {
+		if (g_open[i].which != which || g_open[i].st != st)
+			continue;
+		cudaEvent_t e;
+		if (cudaEventCreate(&e) != cudaSuccess)
+			return;
+		cudaEventRecord(e, st);
+		g_spans.push_back({which, g_open[i].a, e});
+		g_open.erase(g_open.begin() + (long)i);
 		return;
-	cudaEvent_t e;
-	if (cudaEventCreate(&e) != cudaSuccess)
-		return;
-	cudaEventRecord(e, st);
-	g_spans.push_back({which, g_open[which], e});
-	g_open[which] = nullptr;
+	}
 }
 
 namespace {
@@ -110,6 +114,8 @@ struct DeviceCtx {
 	uint32_t *d_statv = nullptr; size_t cap_statv = 0;
 };
 
+std::mutex g_api_mu; // the host entry points run one at a time (they share the per-device streams and grow-only buffers)
+std::atomic<int> g_write_file{-1}; // -1: not set yet ($PIM_SNAPPY_WRITE_FILE), 0 / 1
 std::mutex g_dev_mu;
 std::vector<DeviceCtx> g_devs;
 bool g_devs_ready = false;
@@ -122,27 +128,32 @@ bool device_usable(int id)
 	return p.major >= 10; // the kernels are compiled for sm_100a only
 }
 
+void release_device(DeviceCtx &d)
+{
+	if (d.dev < 0)
+		return;
+	cudaSetDevice(d.dev);
+	if (d.stream) cudaStreamDestroy(d.stream);
+	for (auto &e : d.ev) if (e) cudaEventDestroy(e);
+	cudaFree(d.d_a); cudaFree(d.d_b); cudaFree(d.d_scratch); cudaFree(d.d_off); cudaFree(d.d_status); cudaFree(d.d_statv);
+	if (d.h_small) cudaFreeHost(d.h_small);
+	if (d.h_pin) cudaFreeHost(d.h_pin);
+	if (d.s_in) cudaStreamDestroy(d.s_in);
+	if (d.s_out) cudaStreamDestroy(d.s_out);
+	if (d.stream2) cudaStreamDestroy(d.stream2);
+	for (auto &c : d.cs_more) if (c) cudaStreamDestroy(c);
+	for (auto &e : d.ev_pool) if (e) cudaEventDestroy(e);
+	for (auto &e : d.ev_in) if (e) cudaEventDestroy(e);
+	for (auto &e : d.ev_k) if (e) cudaEventDestroy(e);
+	for (auto &e : d.ev_out) if (e) cudaEventDestroy(e);
+	for (auto &e : d.ev_span) if (e) cudaEventDestroy(e);
+	cudaGetLastError();
+}
+
 int init_devices_locked(const int *ids, int n)
 {
-	for (auto &d : g_devs) {
-		if (d.dev < 0)
-			continue;
-		cudaSetDevice(d.dev);
-		if (d.stream) cudaStreamDestroy(d.stream);
-		for (auto &e : d.ev) if (e) cudaEventDestroy(e);
-		cudaFree(d.d_a); cudaFree(d.d_b); cudaFree(d.d_scratch); cudaFree(d.d_off); cudaFree(d.d_status); cudaFree(d.d_statv);
-		if (d.h_small) cudaFreeHost(d.h_small);
-		if (d.h_pin) cudaFreeHost(d.h_pin);
-		if (d.s_in) cudaStreamDestroy(d.s_in);
-		if (d.s_out) cudaStreamDestroy(d.s_out);
-		if (d.stream2) cudaStreamDestroy(d.stream2);
-		for (auto &c : d.cs_more) if (c) cudaStreamDestroy(c);
-		for (auto &e : d.ev_pool) if (e) cudaEventDestroy(e);
-		for (auto &e : d.ev_in) if (e) cudaEventDestroy(e);
-		for (auto &e : d.ev_k) if (e) cudaEventDestroy(e);
-		for (auto &e : d.ev_out) if (e) cudaEventDestroy(e);
-		for (auto &e : d.ev_span) if (e) cudaEventDestroy(e);
-	}
+	for (auto &d : g_devs)
+		release_device(d);
 	g_devs.clear();
 	std::vector<int> want;
 	if (ids && n > 0) {
@@ -168,19 +179,23 @@ int init_devices_locked(const int *ids, int n)
 		d.dev = id;
 		if (cudaSetDevice(id) != cudaSuccess) continue;
 		if (cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess) continue;
-		for (auto &e : d.ev) cudaEventCreate(&e);
-		if (cudaStreamCreateWithFlags(&d.s_in, cudaStreamNonBlocking) != cudaSuccess) continue;
-		if (cudaStreamCreateWithFlags(&d.s_out, cudaStreamNonBlocking) != cudaSuccess) continue;
-		if (cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking) != cudaSuccess) continue;
-		bool more_ok = true;
-		for (auto &c : d.cs_more) more_ok = more_ok && cudaStreamCreateWithFlags(&c, cudaStreamNonBlocking) == cudaSuccess;
-		if (!more_ok) continue;
-		for (auto &e : d.ev_in) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-		for (auto &e : d.ev_k) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-		for (auto &e : d.ev_out) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-		for (auto &e : d.ev_span) cudaEventCreate(&e);
-		cudaMalloc(&d.d_status, 256);
-		cudaHostAlloc(&d.h_small, 256, cudaHostAllocDefault);
+		bool all = true; // every resource, or the device is not used (what was created is released)
+		for (auto &e : d.ev) all = all && cudaEventCreate(&e) == cudaSuccess;
+		all = all && cudaStreamCreateWithFlags(&d.s_in, cudaStreamNonBlocking) == cudaSuccess;
+		all = all && cudaStreamCreateWithFlags(&d.s_out, cudaStreamNonBlocking) == cudaSuccess;
+		all = all && cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking) == cudaSuccess;
+		for (auto &c : d.cs_more) all = all && cudaStreamCreateWithFlags(&c, cudaStreamNonBlocking) == cudaSuccess;
+		for (auto &e : d.ev_in) all = all && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+		for (auto &e : d.ev_k) all = all && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+		for (auto &e : d.ev_out) all = all && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+		for (auto &e : d.ev_span) all = all && cudaEventCreate(&e) == cudaSuccess;
+		all = all && cudaMalloc(&d.d_status, 256) == cudaSuccess;
+		all = all && cudaHostAlloc(&d.h_small, 256, cudaHostAllocDefault) == cudaSuccess;
+		if (!all) {
+			fprintf(stderr, "pim_snappy: cannot set up CUDA device %d (%s); skipped\n", id, cudaGetErrorString(cudaGetLastError()));
+			release_device(d);
+			continue;
+		}
 		g_devs.push_back(d);
 	}
 	g_devs_ready = true;
@@ -281,6 +296,26 @@ bool get_varint32(const uint8_t *&p, const uint8_t *end, uint32_t *v) // snappy_
 	return false;
 }
 
+// First failed CUDA call of a streamed path, by name (the streams are only synchronised at the end).
+struct CudaCheck {
+	const char *what = nullptr;
+	cudaError_t err = cudaSuccess;
+	void operator()(cudaError_t e, const char *w)
+	{
+		if (e != cudaSuccess && !what) {
+			what = w;
+			err = e;
+		}
+	}
+	bool failed(int dev) const
+	{
+		if (what)
+			fprintf(stderr, "pim_snappy: %s failed on GPU %d: %s\n", what, dev, cudaGetErrorString(err));
+		return what != nullptr;
+	}
+};
+#define CK(call) ck((call), #call)
+
 struct ShardTimes {
 	float copy_in = 0, run = 0, copy_out = 0; // ms
 	double alloc = 0;                         // s
@@ -348,10 +383,12 @@ std::vector<uint64_t> plan_groups(uint64_t total, uint64_t chunk, bool ramp_down
 	return g;
 }
 
-// Compress one shard (a whole number of blocks).  The compressed groups land back to back at
-// host_out.  Returns the shard's compressed bytes in *total.
+// Compress one shard (a whole number of blocks).  host_out != nullptr: the compressed groups land back to
+// back at host_out as soon as each is done.  host_out == nullptr (several GPUs: a shard's place in the file is
+// only known once the shards before it are done): the groups stay on the device, `kept` lists them (device
+// offset in d_b, bytes) for copy_kept_groups().  Returns the shard's compressed bytes in *total.
 int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_bytes, uint32_t block_size, uint8_t *host_out,
-                            uint64_t *total, ShardTimes &tm)
+                            uint64_t *total, ShardTimes &tm, std::vector<std::pair<uint64_t, uint64_t>> *kept = nullptr)
 {
 	const uint64_t nblocks = (in_bytes + block_size - 1) / block_size;
 	const uint64_t cblocks = std::max<uint64_t>(1, chunk_bytes() / block_size);
@@ -377,61 +414,87 @@ int compress_shard_streamed(DeviceCtx &d, const uint8_t *host_in, uint64_t in_by
 	tm.alloc = now_s() - a0;
 	if (!ok)
 		return SNAPPY_BUFFER_TOO_SMALL;
+	CudaCheck ck;
 	// all H2D copies, queued now; event g: group g has arrived
-	cudaEventRecord(d.ev_span[0], d.s_in);
+	CK(cudaEventRecord(d.ev_span[0], d.s_in));
 	for (uint64_t g = 0; g < ng; g++) {
 		const uint64_t lo = blo[g] * block_size, bytes = std::min(in_bytes, blo[g + 1] * block_size) - lo;
-		cudaMemcpyAsync(d.d_a + lo, host_in + lo, bytes, cudaMemcpyHostToDevice, d.s_in);
-		cudaEventRecord(pool_event(d, g), d.s_in);
+		CK(cudaMemcpyAsync(d.d_a + lo, host_in + lo, bytes, cudaMemcpyHostToDevice, d.s_in));
+		CK(cudaEventRecord(pool_event(d, g), d.s_in));
 	}
-	cudaEventRecord(d.ev_span[1], d.s_in);
+	CK(cudaEventRecord(d.ev_span[1], d.s_in));
 	int rc = SNAPPY_OK;
 	uint64_t at = 0; // host offset of the next compressed group
+	bool out_started = false;
 	auto finish = [&](uint64_t g) { // group g's size is known once its kernels are done: queue its D2H
 		if (cudaEventSynchronize(pool_event(d, ng + g)) != cudaSuccess) {
+			ck(cudaGetLastError(), "cudaEventSynchronize(group done)");
 			rc = SNAPPY_INVALID_INPUT;
 			return;
 		}
 		const uint64_t t = d.h_pin[g];
-		if (g == 0)
-			cudaEventRecord(d.ev_span[4], d.s_out);
-		cudaMemcpyAsync(host_out + at, d.d_b + out_at[g], t, cudaMemcpyDeviceToHost, d.s_out);
+		if (host_out) {
+			if (!out_started)
+				CK(cudaEventRecord(d.ev_span[4], d.s_out));
+			out_started = true;
+			CK(cudaMemcpyAsync(host_out + at, d.d_b + out_at[g], t, cudaMemcpyDeviceToHost, d.s_out));
+		} else if (kept) {
+			kept->emplace_back(out_at[g], t);
+		}
 		at += t;
 	};
-	cudaEventRecord(d.ev_span[2], cs[0]);
+	CK(cudaEventRecord(d.ev_span[2], cs[0]));
 	uint64_t finished = 0; // groups whose D2H is queued (in order: the groups land back to back)
-	for (uint64_t g = 0; g < ng && rc == SNAPPY_OK; g++) {
+	for (uint64_t g = 0; g < ng && rc == SNAPPY_OK && !ck.what; g++) {
 		cudaStream_t st = cs[g % NS];
 		const uint64_t lo = blo[g] * block_size, bytes = std::min(in_bytes, blo[g + 1] * block_size) - lo;
-		cudaStreamWaitEvent(st, pool_event(d, g), 0);
+		CK(cudaStreamWaitEvent(st, pool_event(d, g), 0));
 		rc = compress_device_placed(d.d_a + lo, bytes, block_size, d.d_scratch + (g % NS) * scratch_stride, scratch_stride, d.d_b + out_at[g],
 		                            d.d_off + off_at[g], st, false);
-		cudaMemcpyAsync(d.h_pin + g, d.d_off + off_at[g] + groups[g], sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
-		cudaEventRecord(pool_event(d, ng + g), st);
+		CK(cudaMemcpyAsync(d.h_pin + g, d.d_off + off_at[g] + groups[g], sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		CK(cudaEventRecord(pool_event(d, ng + g), st));
 		while (rc == SNAPPY_OK && finished + (uint64_t)(NS - 1) <= g) // keep NS - 1 groups queued behind the running one
 			finish(finished++);
 	}
-	while (rc == SNAPPY_OK && finished < ng)
+	while (rc == SNAPPY_OK && !ck.what && finished < ng)
 		finish(finished++);
-	cudaEventRecord(d.ev_span[5], d.s_out);
+	if (out_started)
+		CK(cudaEventRecord(d.ev_span[5], d.s_out));
 	// span 3 closes the kernels' interval: after every compute stream
 	for (uint64_t g = ng > (uint64_t)NS ? ng - NS : 0; g < ng; g++)
-		cudaStreamWaitEvent(cs[0], pool_event(d, ng + g), 0);
-	cudaEventRecord(d.ev_span[3], cs[0]);
-	bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess;
+		CK(cudaStreamWaitEvent(cs[0], pool_event(d, ng + g), 0));
+	CK(cudaEventRecord(d.ev_span[3], cs[0]));
+	CK(cudaStreamSynchronize(d.s_in));
 	for (int k = 0; k < NS; k++)
-		synced = cudaStreamSynchronize(cs[k]) == cudaSuccess && synced;
-	synced = cudaStreamSynchronize(d.s_out) == cudaSuccess && synced;
-	if (!synced) {
-		fprintf(stderr, "pim_snappy: compress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+		CK(cudaStreamSynchronize(cs[k]));
+	CK(cudaStreamSynchronize(d.s_out));
+	if (ck.failed(d.dev))
 		return SNAPPY_INVALID_INPUT;
-	}
 	if (rc != SNAPPY_OK)
 		return rc;
 	cudaEventElapsedTime(&tm.copy_in, d.ev_span[0], d.ev_span[1]);
 	cudaEventElapsedTime(&tm.run, d.ev_span[2], d.ev_span[3]);
-	cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
+	if (out_started)
+		cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
 	*total = at;
+	return SNAPPY_OK;
+}
+
+// The compressed groups a shard kept on its device, back to back to host_out.
+int copy_kept_groups(DeviceCtx &d, const std::vector<std::pair<uint64_t, uint64_t>> &kept, uint8_t *host_out, ShardTimes &tm)
+{
+	CudaCheck ck;
+	CK(cudaEventRecord(d.ev_span[4], d.s_out));
+	uint64_t at = 0;
+	for (const auto &k : kept) {
+		CK(cudaMemcpyAsync(host_out + at, d.d_b + k.first, k.second, cudaMemcpyDeviceToHost, d.s_out));
+		at += k.second;
+	}
+	CK(cudaEventRecord(d.ev_span[5], d.s_out));
+	CK(cudaStreamSynchronize(d.s_out));
+	if (ck.failed(d.dev))
+		return SNAPPY_INVALID_INPUT;
+	cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
 	return SNAPPY_OK;
 }
 
@@ -449,6 +512,8 @@ __global__ void fetch_offsets_kernel(const uint64_t *__restrict__ host_mapped, u
 int decompress_stream_resident(DeviceCtx &d, const uint8_t *body, uint64_t body_len, uint64_t nblocks, uint32_t block_size,
                                uint64_t out_bytes, uint8_t *host_out, ShardTimes &tm)
 {
+	if (body_len < 5 * nblocks || nblocks == 0)
+		return SNAPPY_INVALID_INPUT; // every block needs its 4-byte size and at least one element byte (a truncated file)
 	const std::vector<uint64_t> pieces = plan_groups(body_len, std::max<uint64_t>(chunk_bytes(), 8), false); // compressed bytes
 	const uint64_t np = pieces.size();
 	const double a0 = now_s();
@@ -462,37 +527,41 @@ int decompress_stream_resident(DeviceCtx &d, const uint8_t *body, uint64_t body_
 	uint64_t *h_off_dev = nullptr;
 	if (cudaHostGetDevicePointer(&h_off_dev, h_off, 0) != cudaSuccess)
 		return SNAPPY_INVALID_INPUT;
+	CudaCheck ck;
 	// all uploads, queued now; event j: bytes [0, pend[j]) have arrived
 	std::vector<uint64_t> pend(np);
-	cudaEventRecord(d.ev_span[0], d.s_in);
+	CK(cudaEventRecord(d.ev_span[0], d.s_in));
 	for (uint64_t j = 0, lo = 0; j < np; j++) {
-		cudaMemcpyAsync(d.d_b + lo, body + lo, pieces[j], cudaMemcpyHostToDevice, d.s_in);
-		cudaEventRecord(pool_event(d, j), d.s_in);
+		CK(cudaMemcpyAsync(d.d_b + lo, body + lo, pieces[j], cudaMemcpyHostToDevice, d.s_in));
+		CK(cudaEventRecord(pool_event(d, j), d.s_in));
 		lo += pieces[j];
 		pend[j] = lo;
 	}
-	cudaEventRecord(d.ev_span[1], d.s_in);
-	cudaMemsetAsync(d.d_statv, 0, np * sizeof(uint32_t), d.stream);
-	cudaEventRecord(d.ev_span[2], d.stream);
+	CK(cudaEventRecord(d.ev_span[1], d.s_in));
+	CK(cudaMemsetAsync(d.d_statv, 0, np * sizeof(uint32_t), d.stream));
+	CK(cudaEventRecord(d.ev_span[2], d.stream));
 
 	int rc = SNAPPY_OK;
 	uint64_t launched = 0; // blocks [0, launched) are on their way
 	bool first_out = true;
+	int64_t last_piece = -1; // last piece a launch was recorded for
 	auto launch = [&](uint64_t bhi, uint64_t piece) { // blocks [launched, bhi) end inside pieces 0..piece
 		if (bhi == launched || rc != SNAPPY_OK)
 			return;
 		const uint64_t blo = launched, nb = bhi - blo;
 		const uint64_t o_lo = blo * (uint64_t)block_size, o_bytes = std::min(out_bytes, bhi * (uint64_t)block_size) - o_lo;
-		cudaStreamWaitEvent(d.stream, pool_event(d, piece), 0);
+		CK(cudaStreamWaitEvent(d.stream, pool_event(d, piece), 0));
 		fetch_offsets_kernel<<<(unsigned)std::min<uint64_t>(64, (nb + 256) / 256), 256, 0, d.stream>>>(h_off_dev + blo, d.d_off + blo, nb + 1);
+		note_launch(1);
 		rc = pim_snappy_decompress_device(d.d_b, d.d_off + blo, nb, block_size, o_bytes, d.d_a + o_lo, d.d_statv + piece, d.stream);
-		cudaEventRecord(pool_event(d, np + piece), d.stream);
-		cudaStreamWaitEvent(d.s_out, pool_event(d, np + piece), 0);
+		CK(cudaEventRecord(pool_event(d, np + piece), d.stream));
+		CK(cudaStreamWaitEvent(d.s_out, pool_event(d, np + piece), 0));
 		if (first_out)
-			cudaEventRecord(d.ev_span[4], d.s_out);
+			CK(cudaEventRecord(d.ev_span[4], d.s_out));
 		first_out = false;
-		cudaMemcpyAsync(host_out + o_lo, d.d_a + o_lo, o_bytes, cudaMemcpyDeviceToHost, d.s_out);
+		CK(cudaMemcpyAsync(host_out + o_lo, d.d_a + o_lo, o_bytes, cudaMemcpyDeviceToHost, d.s_out));
 		launched = bhi;
+		last_piece = (int64_t)piece;
 	};
 	uint64_t pos = 0, piece = 0;
 	for (uint64_t i = 0; i < nblocks && rc == SNAPPY_OK; i++) {
@@ -519,16 +588,17 @@ int decompress_stream_resident(DeviceCtx &d, const uint8_t *body, uint64_t body_
 		h_off[nblocks] = pos;
 		launch(nblocks, np - 1);
 	}
-	cudaEventRecord(d.ev_span[3], d.stream);
-	cudaStreamWaitEvent(d.s_out, pool_event(d, np + np - 1), 0);
-	cudaMemcpyAsync(h_stat, d.d_statv, np * sizeof(uint32_t), cudaMemcpyDeviceToHost, d.s_out);
-	cudaEventRecord(d.ev_span[5], d.s_out);
-	const bool synced = cudaStreamSynchronize(d.s_in) == cudaSuccess && cudaStreamSynchronize(d.stream) == cudaSuccess &&
-	                    cudaStreamSynchronize(d.s_out) == cudaSuccess;
-	if (!synced) {
-		fprintf(stderr, "pim_snappy: decompress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
-		return SNAPPY_INVALID_INPUT;
+	CK(cudaEventRecord(d.ev_span[3], d.stream));
+	if (last_piece >= 0) { // (nothing was launched for a stream that turned out malformed in its first piece)
+		CK(cudaStreamWaitEvent(d.s_out, pool_event(d, np + (uint64_t)last_piece), 0));
+		CK(cudaMemcpyAsync(h_stat, d.d_statv, np * sizeof(uint32_t), cudaMemcpyDeviceToHost, d.s_out));
 	}
+	CK(cudaEventRecord(d.ev_span[5], d.s_out));
+	CK(cudaStreamSynchronize(d.s_in));
+	CK(cudaStreamSynchronize(d.stream));
+	CK(cudaStreamSynchronize(d.s_out));
+	if (ck.failed(d.dev))
+		return SNAPPY_INVALID_INPUT;
 	if (rc != SNAPPY_OK)
 		return rc;
 	for (uint64_t j = 0; j < np; j++)
@@ -536,7 +606,8 @@ int decompress_stream_resident(DeviceCtx &d, const uint8_t *body, uint64_t body_
 			return SNAPPY_INVALID_INPUT;
 	cudaEventElapsedTime(&tm.copy_in, d.ev_span[0], d.ev_span[1]);
 	cudaEventElapsedTime(&tm.run, d.ev_span[2], d.ev_span[3]);
-	cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
+	if (!first_out)
+		cudaEventElapsedTime(&tm.copy_out, d.ev_span[4], d.ev_span[5]);
 	return SNAPPY_OK;
 }
 
@@ -607,6 +678,7 @@ extern "C" void pim_snappy_host_free(void *p)
 
 extern "C" int pim_snappy_set_devices(const int *device_ids, int n)
 {
+	std::lock_guard<std::mutex> api(g_api_mu); // never while an entry point is using the devices
 	std::lock_guard<std::mutex> lk(g_dev_mu);
 	return init_devices_locked(device_ids, n);
 }
@@ -679,7 +751,7 @@ extern "C" void setup_compression(struct host_buffer_context *input, struct host
 	// 4-byte block headers; size for the smallest block size this library accepts being 1 would
 	// be 5n, so the bound is taken for block_size >= 64 and re-checked in snappy_compress_dpu.
 	const size_t n = input->length;
-	const size_t cap = 64 + n + n / 6 + 40 * (n / 64 + 1);
+	const size_t cap = 128 + n + n / 6 + 40 * (n / 64 + 1); // (room for the header beside the streamed path's bound)
 	output->buffer = static_cast<uint8_t *>(pim_snappy_host_alloc(cap));
 	output->curr = output->buffer;
 	output->length = 0;
@@ -715,6 +787,7 @@ extern "C" snappy_status setup_decompression(struct host_buffer_context *input, 
 extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, struct host_buffer_context *output, uint32_t block_size,
                                              struct program_runtime *runtime)
 {
+	std::lock_guard<std::mutex> api(g_api_mu);
 	double t0 = now_s();
 	runtime->d_alloc = runtime->load = runtime->copy_in = runtime->run = runtime->copy_out = runtime->d_free = 0;
 	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE) {
@@ -776,6 +849,17 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 		return SNAPPY_OK;
 	}
 
+	// Several GPUs, large shards: every GPU streams its shard (uploads overlap the kernels) and keeps the
+	// compressed groups on the device until the shards before it are done and its place in the file is known.
+	uint64_t max_shard = 0;
+	for (int g = 0; g < ng; g++) {
+		uint64_t lo, hi;
+		shard_range(nblocks, ng, g, &lo, &hi);
+		max_shard = std::max(max_shard, (hi - lo) * (uint64_t)block_size);
+	}
+	const bool stream_shards = chunk_bytes() && max_shard > 2 * chunk_bytes();
+	std::vector<std::vector<std::pair<uint64_t, uint64_t>>> kept(ng);
+
 	// phase 1: H2D + kernels + read back each shard's compressed size
 	for_each_shard(ng, [&](int g) {
 		DeviceCtx &d = g_devs[g];
@@ -785,23 +869,29 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 		const uint64_t in_bytes = std::min(len, hi * (uint64_t)block_size) - in_lo;
 		const uint64_t nb = hi - lo;
 		cudaSetDevice(d.dev);
+		if (stream_shards) {
+			rc[g] = nb ? compress_shard_streamed(d, input->buffer + in_lo, in_bytes, block_size, nullptr, &total[g], tm[g], &kept[g]) : SNAPPY_OK;
+			return;
+		}
 		const double a0 = now_s();
 		bool ok = grow(d.d_a, d.cap_a, in_bytes + 64) && grow(d.d_b, d.cap_b, pim_snappy_compress_bound(in_bytes, block_size)) &&
 		          grow(d.d_scratch, d.cap_s, pim_snappy_compress_scratch_bytes(in_bytes, block_size)) && grow(d.d_off, d.cap_off, nb + 1);
 		tm[g].alloc = now_s() - a0;
 		if (!ok) { rc[g] = SNAPPY_BUFFER_TOO_SMALL; return; }
-		cudaEventRecord(d.ev[0], d.stream);
-		cudaMemcpyAsync(d.d_a, input->buffer + in_lo, in_bytes, cudaMemcpyHostToDevice, d.stream);
-		cudaEventRecord(d.ev[1], d.stream);
+		CudaCheck ck;
+		CK(cudaEventRecord(d.ev[0], d.stream));
+		CK(cudaMemcpyAsync(d.d_a, input->buffer + in_lo, in_bytes, cudaMemcpyHostToDevice, d.stream));
+		CK(cudaEventRecord(d.ev[1], d.stream));
 		rc[g] = pim_snappy_compress_device(d.d_a, in_bytes, block_size, d.d_scratch, d.cap_s, d.d_b, d.d_off, d.stream);
-		cudaEventRecord(d.ev[2], d.stream);
-		cudaMemcpyAsync(d.h_small, d.d_off + nb, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.stream);
-		if (cudaStreamSynchronize(d.stream) != cudaSuccess) {
-			fprintf(stderr, "pim_snappy: compress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+		CK(cudaEventRecord(d.ev[2], d.stream));
+		CK(cudaMemcpyAsync(d.h_small, d.d_off + nb, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.stream));
+		CK(cudaStreamSynchronize(d.stream));
+		if (ck.failed(d.dev)) {
 			rc[g] = SNAPPY_INVALID_INPUT;
 			return;
 		}
 		total[g] = d.h_small[0];
+		kept[g].assign(1, {0, total[g]});
 		cudaEventElapsedTime(&tm[g].copy_in, d.ev[0], d.ev[1]);
 		cudaEventElapsedTime(&tm[g].run, d.ev[1], d.ev[2]);
 	});
@@ -832,14 +922,7 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 	for_each_shard(ng, [&](int g) {
 		DeviceCtx &d = g_devs[g];
 		cudaSetDevice(d.dev);
-		cudaEventRecord(d.ev[0], d.stream);
-		cudaMemcpyAsync(output->buffer + at[g], d.d_b, total[g], cudaMemcpyDeviceToHost, d.stream);
-		cudaEventRecord(d.ev[1], d.stream);
-		if (cudaStreamSynchronize(d.stream) != cudaSuccess) {
-			rc[g] = SNAPPY_INVALID_INPUT;
-			return;
-		}
-		cudaEventElapsedTime(&tm[g].copy_out, d.ev[0], d.ev[1]);
+		rc[g] = copy_kept_groups(d, kept[g], output->buffer + at[g], tm[g]);
 	});
 	for (int g = 0; g < ng; g++) {
 		if (rc[g] != SNAPPY_OK)
@@ -859,6 +942,7 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input, struct host_buffer_context *output,
                                                struct program_runtime *runtime)
 {
+	std::lock_guard<std::mutex> api(g_api_mu);
 	double t0 = now_s();
 	runtime->d_alloc = runtime->load = runtime->copy_in = runtime->run = runtime->copy_out = runtime->d_free = 0;
 	const uint8_t *end = input->buffer + input->length;
@@ -941,6 +1025,12 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 		const uint64_t o_lo = lo * (uint64_t)block_size;
 		const uint64_t o_bytes = std::min(out_len, hi * (uint64_t)block_size) - o_lo;
 		cudaSetDevice(d.dev);
+		if (nb == 0)
+			return;
+		if (chunk_bytes() && o_bytes > 2 * chunk_bytes()) { // a large shard: upload, kernels and download overlap
+			rc[g] = decompress_stream_resident(d, body + c_lo, c_bytes, nb, block_size, o_bytes, output->buffer + o_lo, tm[g]);
+			return;
+		}
 		const double a0 = now_s();
 		bool ok = grow(d.d_a, d.cap_a, o_bytes + 64) && grow(d.d_b, d.cap_b, c_bytes + 64) && grow(d.d_off, d.cap_off, nb + 1);
 		tm[g].alloc = now_s() - a0;
@@ -948,17 +1038,18 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 		std::vector<uint64_t> rel(nb + 1);
 		for (uint64_t i = 0; i <= nb; i++)
 			rel[i] = off[lo + i] - c_lo;
-		cudaEventRecord(d.ev[0], d.stream);
-		cudaMemcpyAsync(d.d_b, body + c_lo, c_bytes, cudaMemcpyHostToDevice, d.stream);
-		cudaMemcpyAsync(d.d_off, rel.data(), (nb + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d.stream);
-		cudaEventRecord(d.ev[1], d.stream);
+		CudaCheck ck;
+		CK(cudaEventRecord(d.ev[0], d.stream));
+		CK(cudaMemcpyAsync(d.d_b, body + c_lo, c_bytes, cudaMemcpyHostToDevice, d.stream));
+		CK(cudaMemcpyAsync(d.d_off, rel.data(), (nb + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d.stream));
+		CK(cudaEventRecord(d.ev[1], d.stream));
 		rc[g] = pim_snappy_decompress_device(d.d_b, d.d_off, nb, block_size, o_bytes, d.d_a, d.d_status, d.stream);
-		cudaEventRecord(d.ev[2], d.stream);
-		cudaMemcpyAsync(output->buffer + o_lo, d.d_a, o_bytes, cudaMemcpyDeviceToHost, d.stream);
-		cudaMemcpyAsync(d.h_small + 1, d.d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, d.stream);
-		cudaEventRecord(d.ev[3], d.stream);
-		if (cudaStreamSynchronize(d.stream) != cudaSuccess) {
-			fprintf(stderr, "pim_snappy: decompress failed on GPU %d: %s\n", d.dev, cudaGetErrorString(cudaGetLastError()));
+		CK(cudaEventRecord(d.ev[2], d.stream));
+		CK(cudaMemcpyAsync(output->buffer + o_lo, d.d_a, o_bytes, cudaMemcpyDeviceToHost, d.stream));
+		CK(cudaMemcpyAsync(d.h_small + 1, d.d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, d.stream));
+		CK(cudaEventRecord(d.ev[3], d.stream));
+		CK(cudaStreamSynchronize(d.stream));
+		if (ck.failed(d.dev)) {
 			rc[g] = SNAPPY_INVALID_INPUT;
 			return;
 		}
@@ -981,11 +1072,32 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 	return SNAPPY_OK;
 }
 
-// the reference's names
+extern "C" void pim_snappy_set_write_file(int enable) { g_write_file.store(enable ? 1 : 0); }
+
+// The reference's names.  Its DPU compressor writes output->file_name itself (snappy_compress.c:626-627,697-703) and its
+// main() then skips write_output_host (dpu_snappy.c:209); with pim_snappy_set_write_file(1) / $PIM_SNAPPY_WRITE_FILE=1
+// this entry point does the same, so that the reference's UNMODIFIED main() produces the file.
 extern "C" snappy_status snappy_compress_dpu(struct host_buffer_context *input, struct host_buffer_context *output, uint32_t block_size,
                                              struct program_runtime *runtime)
 {
-	return snappy_compress_gpu(input, output, block_size, runtime);
+	const snappy_status rc = snappy_compress_gpu(input, output, block_size, runtime);
+	int wf = g_write_file.load();
+	if (wf < 0) {
+		const char *e = getenv("PIM_SNAPPY_WRITE_FILE");
+		wf = e && atoi(e) != 0 ? 1 : 0;
+		g_write_file.store(wf);
+	}
+	if (rc == SNAPPY_OK && wf == 1 && output->file_name) {
+		FILE *f = fopen(output->file_name, "w");
+		if (!f || fwrite(output->buffer, 1, output->length, f) != output->length) {
+			fprintf(stderr, "pim_snappy: cannot write %s\n", output->file_name);
+			if (f)
+				fclose(f);
+			return SNAPPY_INVALID_INPUT;
+		}
+		fclose(f);
+	}
+	return rc;
 }
 
 extern "C" snappy_status snappy_decompress_dpu(struct host_buffer_context *input, struct host_buffer_context *output,
