@@ -103,6 +103,9 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 	const int lane = lane_id();
 	const bool parser = role == 0; // else emitter
 	const int ptid = (int)role * 32 + lane;
+	uint32_t seq = 0; // records this warp has published (parser) / consumed (emitter) so far
+	if (ptid == 0)
+		ring_init(ring);
 	for (;;) {
 		if (ptid == 0)
 			*mail = atomicAdd(a.counter, 1u);
@@ -133,16 +136,12 @@ __device__ PIM_PAIR_INLINE void compress_pair(const CompressArgs &a, uint8_t *tb
 				asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc + i));
 		for (uint32_t i = ptid * 16u; i < 2u * ts; i += 1024u) // get_hash_table, snappy_compress.c:139-146
 			*reinterpret_cast<uint4 *>(tbytes + i) = make_uint4(0, 0, 0, 0);
-		if (ptid == 0) {
-			ring->head = 0;
-			ring->tail = 0;
-		}
 		bar_sync(bar_id, 64);
 
 		if (parser) { // the block's serial chain
-			parse_block_warp<GT>(c, ring);
+			parse_block_warp<GT>(c, ring, seq);
 		} else { // output bytes only
-			const uint32_t o = emit_block_warp(c, ring);
+			const uint32_t o = emit_block_warp(c, ring, seq);
 			if (lane == 0)
 				sa.sizes[blk] = o;
 		}

@@ -361,17 +361,59 @@ struct EmitRec {
 	uint32_t pad[7];    // (192-byte records: measurably faster than packed ones; pad[0] of record 0 carries the pair's block index)
 };
 
+// Hand-off protocol.  On the device every slot has two mbarriers: `full` (the 32 parser lanes arrive after writing the
+// record, the emitter lanes block in mbarrier.try_wait until the phase completes) and `empty` (the other way round), so
+// a waiting warp sleeps in hardware instead of polling shared memory -- in round 1 the emitters' poll loop was a quarter
+// of all issued instructions.  The record counters run over the whole kernel (phase parity = (count / CW_RING) & 1).
+// On the emulator the two counters live in the ring and the warps poll them.
 struct EmitRing {
 	EmitRec rec[CW_RING];
+#ifdef PIM_WARP_EMU
 	volatile uint32_t head; // records published by the parser
 	volatile uint32_t tail; // records consumed by the emitter
+#else
+	unsigned long long full[CW_RING], empty[CW_RING];
+#endif
 };
+
+#ifndef PIM_WARP_EMU
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity)
+{
+	asm volatile("{\n"
+	             ".reg .pred p;\n"
+	             "LAB_WAIT:\n"
+	             "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	             "@p bra LAB_DONE;\n"
+	             "bra LAB_WAIT;\n"
+	             "LAB_DONE:\n"
+	             "}" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+PW_FN void ring_init(EmitRing *ring) // by one thread, before the pair's first barrier
+{
+	for (uint32_t i = 0; i < CW_RING; i++) {
+		mbar_init(&ring->full[i], 32);
+		mbar_init(&ring->empty[i], 32);
+	}
+}
+#endif
 
 PW_FN void ring_push(EmitRing *ring, uint32_t &head, uint32_t lanew, uint32_t L, uint32_t H, uint32_t V, uint32_t satbit, uint32_t lit_from,
                      uint32_t lit_len, uint32_t copy_off, uint32_t copy_len, uint32_t done, int lane)
 {
+#ifdef PIM_WARP_EMU
 	while (head - ring->tail >= CW_RING)
 		wp::spin_pause();
+#else
+	mbar_wait(&ring->empty[head % CW_RING], ((head / CW_RING) & 1u) ^ 1u); // (passes at once the first time round)
+#endif
 	EmitRec &r = ring->rec[head % CW_RING];
 	r.lanew[lane] = lanew;
 	if (lane == 0) {
@@ -385,15 +427,21 @@ PW_FN void ring_push(EmitRing *ring, uint32_t &head, uint32_t lanew, uint32_t L,
 		r.copy_len = copy_len;
 		r.done = done;
 	}
+#ifdef PIM_WARP_EMU
 	wp::fence_block();
 	wp::syncwarp();
 	head++;
 	if (lane == 0)
 		ring->head = head;
+#else
+	mbar_arrive(&ring->full[head % CW_RING]); // release: my stores above are visible to whoever sees the phase complete
+	head++;
+#endif
 }
 
 // Emitter warp: turns the parser's records into output bytes.  Returns the bytes written (4 + elements).
-PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring)
+// `tail`: records consumed so far by this pair (runs over the whole kernel on the device).
+PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring, uint32_t &tail)
 {
 	using namespace cw;
 	const int lane = wp::lane();
@@ -401,17 +449,25 @@ PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring)
 	const uint32_t lt = mybit - 1u;
 	const uint32_t le = lt | mybit;
 	uint32_t o = 4; // output cursor (4 bytes reserved for the size, :291)
-	for (uint32_t tail = 0;; tail++) {
+	for (;; tail++) {
+#ifdef PIM_WARP_EMU
 		while (ring->head == tail)
 			wp::spin_pause();
 		wp::fence_block();
+#else
+		mbar_wait(&ring->full[tail % CW_RING], (tail / CW_RING) & 1u);
+#endif
 		const EmitRec &r = ring->rec[tail % CW_RING];
 		const uint32_t lanew = r.lanew[lane];
 		const uint32_t L = r.L, H = r.H, V = r.V, satbit = r.satbit, lit_from = r.lit_from, lit_len = r.lit_len, copy_off = r.copy_off,
 		               copy_len = r.copy_len, done = r.done;
+#ifdef PIM_WARP_EMU
 		wp::syncwarp();
 		if (lane == 0)
 			ring->tail = tail + 1; // the slot may be reused
+#else
+		mbar_arrive(&ring->empty[tail % CW_RING]); // (my loads above are done: their values are in registers)
+#endif
 		if (lit_len) // :355 / :405-409
 			o = emit_literal(c, o, lit_from, lit_len, lane);
 		const uint32_t LS = L & (V << 1); // first byte of each in-window literal
@@ -447,8 +503,10 @@ PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring)
 		}
 		if (copy_len)
 			o = emit_copy(c, o, copy_off, copy_len, lane);
-		if (done)
+		if (done) {
+			tail++;
 			break;
+		}
 	}
 	if (lane < 4) // :411
 		c.out[lane] = (uint8_t)((o - 4) >> (8 * lane));
@@ -458,7 +516,8 @@ PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring)
 // Parser warp: runs the passes of one block and publishes one record per pass.
 // GT: the hash table lives in global memory (L2) instead of shared memory.
 template <bool GT>
-PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
+// `head`: records published so far by this pair (runs over the whole kernel on the device).
+PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 {
 	using namespace cw;
 	const int lane = wp::lane();
@@ -467,7 +526,6 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring)
 	const uint32_t le = lt | mybit;
 	const uint32_t n = c.n;
 	uint32_t emit = 0; // first input byte not yet emitted (next_emit)
-	uint32_t head = 0; // records published so far
 	uint32_t pf = 0;   // input below this position has been prefetched into L2
 
 	if (n >= CW_MARGIN) {

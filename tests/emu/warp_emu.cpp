@@ -190,13 +190,14 @@ struct Job {
 void body(void *arg)
 {
 	Job *j = static_cast<Job *>(arg);
+	uint32_t seq = 0; // records of this block (the emulator's ring counters restart with every block)
 	if (g_cur < NL) {
 		if (g_global_table)
-			pimsnappy::parse_block_warp<true>(j->blk, &j->ring); // the code path of the pairs whose table lives in global memory
+			pimsnappy::parse_block_warp<true>(j->blk, &j->ring, seq); // the code path of the pairs whose table lives in global memory
 		else
-			pimsnappy::parse_block_warp<false>(j->blk, &j->ring);
+			pimsnappy::parse_block_warp<false>(j->blk, &j->ring, seq);
 	} else {
-		const uint32_t r = pimsnappy::emit_block_warp(j->blk, &j->ring);
+		const uint32_t r = pimsnappy::emit_block_warp(j->blk, &j->ring, seq);
 		if (pimsnappy::wp::lane() == 0)
 			j->result = r;
 	}
