@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-mib", type=int, default=1024, help="cpu_baseline sample size (1 thread)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-by-input", dest="by_input", action="store_false", help="skip the text / corpus / binary one-launch measurements")
     return ap.parse_args()
 
 
@@ -128,17 +129,36 @@ def cpu_baseline_1thread(P, args):
             "compress_gbps": n / (t1 - t0) / 1e9, "decompress_gbps": n / (t2 - t1) / 1e9}
 
 
+def host_cores():
+    """(threads this process may run on, distinct physical cores among them) -- the second from /proc/cpuinfo."""
+    aff = sorted(os.sched_getaffinity(0))
+    phys = set()
+    try:
+        cur = {}
+        for ln in open("/proc/cpuinfo"):
+            if ":" in ln:
+                k, v = [x.strip() for x in ln.split(":", 1)]
+                cur[k] = v
+            elif cur:
+                if int(cur.get("processor", -1)) in aff:
+                    phys.add((cur.get("physical id", "0"), cur.get("core id", cur.get("processor"))))
+                cur = {}
+    except Exception:
+        pass
+    return len(aff), (len(phys) if phys else None)
+
+
 def run_reference_arm(args):
-    """--impl reference: the reference's host codec on all host threads (rank 0 only)."""
+    """--impl reference: the reference's host codec on all host threads (rank 0 only).  Loads oracle/_ref and the
+    workload generator library only -- no codec of this repository is in the process."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     import pim_compression_b200 as P
     from concurrent.futures import ThreadPoolExecutor
-    P.lib()
     codec, kind = cpu_codec()
-    cores = len(os.sched_getaffinity(0))
-    slice_bytes = 32 << 20  # one independent stream slice per thread per step
+    cores, phys = host_cores()
+    slice_bytes = 32 << 20  # thread t codes the first 32 MiB of stream t of the corpus, every step
     slices = [P.synth_host(P.SYNTH_MIX, SEED_BASE + t, slice_bytes) for t in range(cores)]
 
     def work(d):
@@ -157,10 +177,12 @@ def run_reference_arm(args):
                 times.append(dt)
     t = sum(times) / len(times)
     v = total / t / 1e9
-    sample = f"{cores} threads x {slice_bytes >> 20} MiB SYN-MIX slices per step, compress + decompress each (ctypes releases the GIL)"
+    sample = (f"{cores} threads ({phys if phys else '?'} physical cores; the reference codec is single-threaded, one independent slice per thread) x "
+              f"the first {slice_bytes >> 20} MiB of streams 0..{cores - 1} of the corpus per step, compress + decompress each (ctypes releases the GIL)")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u8", "data": "synthetic", "config": {"workload": workload_name(args, args.gpus)},
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(args, args.gpus), "cpu_sample_bytes_per_step": total, "threads": cores, "physical_cores": phys},
             "cpu_baseline": {"value": v, "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line))
@@ -277,6 +299,12 @@ def run_ours(args):
     sync_all()
     dev_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     clocks = sampler.stop()
+    # what the LAST timed step left behind is checked too (the warm-up check zeroed d_back): every stream's status word,
+    # compressed size and round trip
+    assert int(d_status.abs().sum().item()) == 0, "malformed stream reported in the timed steps"
+    assert sum(int(d_off[s][-1].item()) for s in range(S)) == comp_bytes, "compressed size changed in the timed steps"
+    for s in range(S):
+        assert torch.equal(d_back[s], d_in[s]), f"round trip of the timed steps failed on stream {s}"
     launches = P.launch_count() - launches0
     prof = P.profile_read()
     P.profile(False)
@@ -391,6 +419,66 @@ def run_ours(args):
                "pinned_copy": pcie,
                "api": "snappy_compress_dpu + snappy_decompress_dpu (C ABI) on page-locked host buffers, one GPU per rank"}
 
+    # ---- several GPUs serving ONE stream through the C ABI (contiguous block ranges per GPU, host stitch): rank 0 alone,
+    # the other ranks parked at the barrier
+    e2e_sharded = None
+    if world > 1 and not args.no_e2e:
+        sync_all()
+        if rank == 0:
+            def one_stream():
+                t0 = time.perf_counter()
+                clen = e2e_stream(0)
+                return clen, time.perf_counter() - t0
+            assert P.set_devices(list(range(world))) == world
+            one_stream()
+            times = []
+            for _ in range(3):
+                clen_n, dt1 = one_stream()
+                times.append(dt1)
+            comp_n = h_comp.array[:clen_n].copy()
+            back_ok = bool(np.array_equal(h_back.array[:n], h_in[0].array))
+            assert P.set_devices([local_rank]) == 1
+            clen_1, _ = one_stream()
+            e2e_sharded = {"value": n / min(times) / 1e9, "unit": "GB/s", "n_gpus": world, "stream_bytes": n,
+                           "bytes_equal_to_1gpu": bool(clen_1 == clen_n and np.array_equal(h_comp.array[:clen_1], comp_n)) and back_ok,
+                           "api": "snappy_compress_dpu + snappy_decompress_dpu on ONE stream with pim_snappy_set_devices([0..N-1]), best of 3"}
+        sync_all()
+
+    # ---- the same two kernels on other inputs (one 1-stream launch each, after one warm launch): text, the reference's
+    # fixtures tiled to the stream size, the binary-like mix
+    by_input = None
+    if rank == 0 and args.by_input:
+        import gzip
+        gold = os.path.join(ROOT, "tests", "golden")
+        def corpus_fill():
+            parts = [np.frombuffer(gzip.open(os.path.join(gold, f + ".txt.gz"), "rb").read(), dtype=np.uint8) for f in ("world192", "plrabn12", "terror2")]
+            xml = P.decompress(np.frombuffer(gzip.open(os.path.join(gold, "xml.snappy.gz"), "rb").read(), dtype=np.uint8))  # (xml.txt is not shipped)
+            p = np.concatenate(parts + [xml])
+            d_in[0].copy_(torch.from_numpy(np.tile(p, n // p.size + 1)[:n]))
+        fills = {"SYN-TEXT": lambda: P.synth_device(P.SYNTH_TEXT, 0x5BA0, d_in[0].data_ptr(), n, st),
+                 "CORPUS (world192+plrabn12+terror2+xml tiled)": corpus_fill,
+                 "SYN-BIN": lambda: P.synth_device(P.SYNTH_BIN, 0x0B1A, d_in[0].data_ptr(), n, st)}
+        by_input = {}
+        for name, fill in fills.items():
+            fill()
+            torch.cuda.synchronize()
+            P.profile(True)
+            for r in range(2):
+                P.profile_read()
+                P.compress_device(d_in[0].data_ptr(), n, bs, scratch[0].data_ptr(), scratch[0].numel(), d_comp[0].data_ptr(), d_off[0].data_ptr(), st)
+                P.decompress_device(d_comp[0].data_ptr(), d_off[0].data_ptr(), nb, bs, n, d_back[0].data_ptr(), d_status.data_ptr(), st)
+                torch.cuda.synchronize()
+                pr = P.profile_read()
+            P.profile(False)
+            assert int(d_status[0].item()) == 0 and torch.equal(d_back[0], d_in[0]), f"round trip failed on {name}"
+            cb = int(d_off[0][-1].item())
+            row = {"stream_bytes": n, "compressed_fraction": cb / n}
+            for k in ("compress", "decompress"):
+                ms = pr[k]["ms"]
+                row[k] = {"ms": ms, "uncompressed_gbps": n / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": (n + cb) / (ms * 1e-3) / 1e9 / peak}
+            row["compress"]["scan_compact_ms"] = pr["scan"]["ms"] + pr["compact"]["ms"]
+            by_input[name] = row
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_1thread(P, args)
@@ -401,8 +489,8 @@ def run_ours(args):
                 "data": "synthetic",
                 "config": {"workload": workload_name(args, world), "l2": f"inputs ({U / GIB:g} GiB per GPU, every stream read once per step) far exceed the 126 MB L2; no flush needed",
                            "compressed_fraction": comp_bytes / U, "bytes_per_gpu": U},
-                "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-                "clocks": clocks}
+                "roofline": roofline, "kernels": kern, "by_input": by_input, "cpu_baseline": cpu, "e2e": e2e, "e2e_sharded": e2e_sharded,
+                "gpu_launches": int(launches), "clocks": clocks}
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)

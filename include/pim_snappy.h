@@ -205,15 +205,6 @@ int pim_snappy_profile_read(double ms[4], uint64_t n[4]);
  * (bench.py reports the difference over the timed region as gpu_launches). */
 uint64_t pim_snappy_launch_count(void);
 
-/* ------------------------------------------------------------------------
- * Part 3 -- seeded integer-only workload generators (bit-identical on host
- * and device; definitions in DESIGN.md).  kind: 0 text-like, 1 random,
- * 2 mixed (1 MiB text / 1 MiB random alternating), 3 binary-like mix.
- * ---------------------------------------------------------------------- */
-enum { PIM_SYNTH_TEXT = 0, PIM_SYNTH_RANDOM = 1, PIM_SYNTH_MIX = 2, PIM_SYNTH_BIN = 3 };
-int pim_snappy_synth_host(int kind, uint64_t seed, uint8_t *out, uint64_t n);
-int pim_snappy_synth_device(int kind, uint64_t seed, uint8_t *d_out, uint64_t n, void *stream);
-
 const char *pim_snappy_version(void);
 
 #ifdef __cplusplus

@@ -22,6 +22,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(_HERE, "_build", "liboracle.so")
 REF_SO = os.path.join(_HERE, "_ref", "libsnappy_ref.so")
 REF_BIN = os.path.join(_HERE, "_ref", "dpu_snappy_ref")
+REFMAIN_BIN = os.path.join(_HERE, "_ref", "dpu_snappy_refmain")  # the reference's main() linked against libpim_snappy.so
 REFERENCE_ROOT = "/root/reference"
 
 OK, INVALID_INPUT, BUFFER_TOO_SMALL = 0, 1, 2
@@ -34,6 +35,8 @@ def build(with_ref: bool | None = None) -> None:
         with_ref = os.path.isdir(os.path.join(REFERENCE_ROOT, "snappy"))
     if with_ref:
         subprocess.run(["make", "-s", "-C", _HERE, "ref"], check=True)
+        if os.path.exists(os.path.join(_HERE, "..", "pim-compression_b200", "libpim_snappy.so")):
+            subprocess.run(["make", "-s", "-C", _HERE, "refmain"], check=True)  # the reference's main() bound to the product library
 
 
 def _u8(buf) -> np.ndarray:

@@ -8,6 +8,7 @@ no CPU fallback (loading fails loudly if ``libpim_snappy.so`` has not been built
 Import name: ``pim_compression_b200`` (the directory name carries a hyphen; the repo root has a
 one-file import shim).
 """
+from . import api  # noqa: F401
 from .api import (  # noqa: F401
     LIB_PATH,
     SNAPPY_OK,
@@ -30,6 +31,7 @@ from .api import (  # noqa: F401
     decompress_device,
     gather_shards,
     block_offsets,
+    synth_lib,
     synth_host,
     synth_device,
     set_devices,

@@ -15,6 +15,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpim_snappy.so")
+SYNTH_LIB_PATH = os.path.join(_HERE, "libpim_synth.so")  # workload generators (include/pim_synth.h): no codec inside
 
 SNAPPY_OK, SNAPPY_INVALID_INPUT, SNAPPY_BUFFER_TOO_SMALL = 0, 1, 2
 SYNTH_TEXT, SYNTH_RANDOM, SYNTH_MIX, SYNTH_BIN = 0, 1, 2, 3
@@ -88,8 +89,6 @@ def lib() -> C.CDLL:
         "pim_snappy_launch_count": (C.c_uint64, []),
         "pim_snappy_profile": (None, [C.c_int]),
         "pim_snappy_profile_read": (C.c_int, [P(C.c_double), P(C.c_uint64)]),
-        "pim_snappy_synth_host": (C.c_int, [C.c_int, C.c_uint64, C.c_void_p, C.c_uint64]),
-        "pim_snappy_synth_device": (C.c_int, [C.c_int, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]),
         "pim_snappy_version": (C.c_char_p, []),
         "get_runtime": (C.c_double, [C.c_void_p, C.c_void_p]),
     }
@@ -106,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_set_chunk_bytes", "pim_snappy_set_write_file", "pim_snappy_shard_range", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
     "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_decompress_device", "pim_snappy_compress_batch_device",
     "pim_snappy_decompress_batch_device", "pim_snappy_gather_shards",
-    "pim_snappy_launch_count", "pim_snappy_profile", "pim_snappy_profile_read", "pim_snappy_synth_host", "pim_snappy_synth_device", "pim_snappy_version",
+    "pim_snappy_launch_count", "pim_snappy_profile", "pim_snappy_profile_read", "pim_snappy_version",
 ]
 
 
@@ -295,16 +294,34 @@ def decompress_device(d_comp_ptr: int, d_off_ptr: int, nblocks: int, block_size:
         raise SnappyError(st, "pim_snappy_decompress_device")
 
 
+_synth = None
+
+
+def synth_lib() -> C.CDLL:
+    """libpim_synth.so: the seeded workload generators (no codec; the reference arm of bench.py loads only this)."""
+    global _synth
+    if _synth is None:
+        if not os.path.exists(SYNTH_LIB_PATH):
+            raise ImportError(f"{SYNTH_LIB_PATH} is not built; run `make -C pim-compression_b200`")
+        S = C.CDLL(SYNTH_LIB_PATH)
+        S.pim_snappy_synth_host.restype = C.c_int
+        S.pim_snappy_synth_host.argtypes = [C.c_int, C.c_uint64, C.c_void_p, C.c_uint64]
+        S.pim_snappy_synth_device.restype = C.c_int
+        S.pim_snappy_synth_device.argtypes = [C.c_int, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]
+        _synth = S
+    return _synth
+
+
 def synth_host(kind: int, seed: int, n: int, out: np.ndarray | None = None) -> np.ndarray:
     buf = out if out is not None else np.empty(n, dtype=np.uint8)
     assert buf.size >= n and buf.dtype == np.uint8
-    rc = lib().pim_snappy_synth_host(kind, seed, buf.ctypes.data, n)
+    rc = synth_lib().pim_snappy_synth_host(kind, seed, buf.ctypes.data, n)
     if rc:
         raise ValueError("pim_snappy_synth_host")
     return buf[:n]
 
 
 def synth_device(kind: int, seed: int, d_ptr: int, n: int, stream: int = 0) -> None:
-    rc = lib().pim_snappy_synth_device(kind, seed, d_ptr, n, stream)
+    rc = synth_lib().pim_snappy_synth_device(kind, seed, d_ptr, n, stream)
     if rc:
         raise ValueError("pim_snappy_synth_device")

@@ -24,7 +24,11 @@
 #include <mutex>
 #include <cstring>
 
-#include "common.cuh"
+#include <cstdint>
+#include <algorithm>
+#include <cuda_runtime.h>
+
+#include "../../include/pim_synth.h"
 
 namespace pimsnappy {
 namespace {

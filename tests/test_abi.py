@@ -28,6 +28,36 @@ def test_exports_match_header(P):
         assert re.search(rf"\bT {name}\b", out), name
 
 
+def test_synth_library_is_separate(P):
+    """include/pim_synth.h is served by libpim_synth.so, not by the codec library (bench.py's reference arm loads only it)."""
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "pim_synth.h")).read(), flags=re.S)
+    declared = set(re.findall(r"\b([a-z_0-9]+)\s*\([^;{]*\)\s*;", hdr))
+    assert declared == {"pim_snappy_synth_host", "pim_snappy_synth_device"}
+    nm = lambda path: subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True, check=True).stdout
+    synth, codec = nm(P.api.SYNTH_LIB_PATH), nm(P.LIB_PATH)
+    for name in declared:
+        assert re.search(rf"\bT {name}\b", synth), name
+        assert name not in codec
+    assert "snappy_compress" not in synth and "snappy_decompress" not in synth
+
+
+def test_out_of_domain_lengths_rejected_before_any_device_work(P):
+    """Streams of 4 GiB and more do not exist in the format (varint32 lengths, snappy_compress.c:461):
+    rejected with SNAPPY_BUFFER_TOO_SMALL, and so is a block size above 65536, before a buffer or a device is touched."""
+    L = P.lib()
+    inp, out, rt = P.HostBufferContext(), P.HostBufferContext(), P.ProgramRuntime()
+    dummy = (C.c_uint8 * 16)()
+    inp.buffer = inp.curr = C.addressof(dummy)
+    out.buffer = out.curr = C.addressof(dummy)
+    inp.max = out.max = 2**63
+    inp.length = 1 << 32
+    assert L.snappy_compress_dpu(C.byref(inp), C.byref(out), 32768, C.byref(rt)) == P.SNAPPY_BUFFER_TOO_SMALL
+    inp.length = 10
+    assert L.snappy_compress_dpu(C.byref(inp), C.byref(out), 65537, C.byref(rt)) == P.SNAPPY_BUFFER_TOO_SMALL
+    assert L.snappy_compress_dpu(C.byref(inp), C.byref(out), 0, C.byref(rt)) == P.SNAPPY_BUFFER_TOO_SMALL
+    assert bytes(dummy) == bytes(16)
+
+
 def test_struct_layout(P):
     # dpu_snappy.h:37-55 on LP64: 5 x 8 bytes and 7 doubles
     assert C.sizeof(P.HostBufferContext) == 40
