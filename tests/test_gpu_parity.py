@@ -275,6 +275,14 @@ def test_streamed_host_path_matches_single_shot(P, oracle):
         bad[hdr + int(off[-3]) + 4] = 0xFF  # copy4 tag with a wild offset at the start of a late block
         with pytest.raises(P.SnappyError):
             P.decompress(bad)
+        # a header that promises far more output than the (truncated) file holds must come back as an error, not hang
+        # (streamed path: declared length > 2 chunks; round-1 advisor finding)
+        for body in (b"", b"\x05\x00\x00", b"\x05\x00\x00\x00" + bytes([4 << 2]) + b"abcde"):
+            s = np.frombuffer(b"\x80\x80\x80\x20" + b"\x80\x80\x02" + body, dtype=np.uint8)  # dlen = 64 MiB, 32 KiB blocks
+            with pytest.raises(P.SnappyError) as e:
+                P.decompress(s)
+            assert e.value.status == P.SNAPPY_INVALID_INPUT
+        assert np.array_equal(P.decompress(oracle.compress(data, 32768)), data)  # still healthy
     finally:
         P.set_chunk_bytes(32 << 20)  # the library's default
 
@@ -292,14 +300,23 @@ def test_multi_gpu_shards_match_single_gpu(P, oracle):
             want = oracle.compress(data, bs)
             for n in sorted({2, ndev}):
                 assert P.set_devices(list(range(n))) == n
-                got = P.compress(data, bs)
-                assert got.size == want.size and np.array_equal(got, want), (bs, n)
-                assert np.array_equal(P.decompress(want), data), (bs, n)
+                for chunk in (0, 1 << 20):  # every shard in one piece / every GPU streams its shard in groups
+                    P.set_chunk_bytes(chunk)
+                    got = P.compress(data, bs)
+                    assert got.size == want.size and np.array_equal(got, want), (bs, n, chunk)
+                    assert np.array_equal(P.decompress(want), data), (bs, n, chunk)
+        P.set_chunk_bytes(1 << 20)
+        bad = oracle.compress(data, 32768).copy()  # a malformed block in the last GPU's shard is still reported
+        _, _, _, off = P.block_offsets(bad)
+        bad[bad.size - int(off[-1]) + int(off[-3]) + 4] = 0xFF
+        with pytest.raises(P.SnappyError):
+            P.decompress(bad)
         # fewer blocks than GPUs
         tiny = data[:40000]
         assert np.array_equal(P.compress(tiny, 32768), oracle.compress(tiny, 32768))
         assert np.array_equal(P.decompress(oracle.compress(tiny, 32768)), tiny)
     finally:
+        P.set_chunk_bytes(32 << 20)
         P.set_devices([0])
 
 
