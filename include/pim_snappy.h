@@ -134,6 +134,16 @@ void pim_snappy_set_chunk_bytes(uint64_t bytes);
 /* Largest block size of the format's valid domain. */
 #define PIM_SNAPPY_MAX_BLOCK_SIZE 65536u
 
+/* Extended-domain mode (BASELINE.json config 3 sweeps block sizes up to 1 MB).  Above 65,536 bytes
+ * per block the reference's host compressor still runs, but its 16-bit hash-table entries (snappy_compress.c:139,347,
+ * 392,397) and 16-bit copy offsets (:241-243) make it emit streams that NO decoder reproduces the input from -- its own
+ * included.  With enable != 0 (or $PIM_SNAPPY_EXTENDED_BLOCKS=1) the COMPRESSOR accepts block sizes up to
+ * PIM_SNAPPY_MAX_EXTENDED_BLOCK_SIZE and reproduces the reference's bytes there too, truncations included, so that
+ * compressed sizes / ratios of the reference's sweep can be reproduced.  The decoder is untouched: it keeps rejecting
+ * block sizes above 65,536 (SNAPPY_BUFFER_TOO_SMALL).  Default: off. */
+#define PIM_SNAPPY_MAX_EXTENDED_BLOCK_SIZE 1048576u
+void pim_snappy_set_extended_blocks(int enable);
+
 /* ------------------------------------------------------------------------
  * Part 2 -- device-resident batched API (current device, caller's stream)
  *

@@ -36,6 +36,7 @@ from .api import (  # noqa: F401
     synth_device,
     set_devices,
     set_chunk_bytes,
+    set_extended_blocks,
     shard_range,
     device_count,
     launch_count,

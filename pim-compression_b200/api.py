@@ -74,6 +74,7 @@ def lib() -> C.CDLL:
         "pim_snappy_device_count": (C.c_int, []),
         "pim_snappy_set_chunk_bytes": (None, [C.c_uint64]),
         "pim_snappy_set_write_file": (None, [C.c_int]),
+        "pim_snappy_set_extended_blocks": (None, [C.c_int]),
         "pim_snappy_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
         "pim_snappy_num_blocks": (C.c_uint64, [C.c_uint64, C.c_uint32]),
         "pim_snappy_compress_bound": (C.c_uint64, [C.c_uint64, C.c_uint32]),
@@ -102,7 +103,7 @@ def lib() -> C.CDLL:
 EXPORTED_SYMBOLS = [
     "setup_compression", "setup_decompression", "snappy_compress_dpu", "snappy_decompress_dpu",
     "snappy_compress_gpu", "snappy_decompress_gpu", "get_runtime", "pim_snappy_host_alloc", "pim_snappy_host_free",
-    "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_set_chunk_bytes", "pim_snappy_set_write_file", "pim_snappy_shard_range", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
+    "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_set_chunk_bytes", "pim_snappy_set_write_file", "pim_snappy_set_extended_blocks", "pim_snappy_shard_range", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
     "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_decompress_device", "pim_snappy_compress_batch_device",
     "pim_snappy_decompress_batch_device", "pim_snappy_gather_shards",
     "pim_snappy_launch_count", "pim_snappy_profile", "pim_snappy_profile_read", "pim_snappy_version",
@@ -124,6 +125,11 @@ def shard_range(nblocks: int, n_shards: int, shard: int) -> tuple[int, int]:
 def set_chunk_bytes(n: int) -> None:
     """Chunk size of the streamed host path (0: whole shard in one piece)."""
     lib().pim_snappy_set_chunk_bytes(n)
+
+
+def set_extended_blocks(enable: bool) -> None:
+    """Extended-domain mode of the compressor (block sizes up to 1 MiB, the reference's bytes incl. its 16-bit truncations)."""
+    lib().pim_snappy_set_extended_blocks(1 if enable else 0)
 
 
 def device_count() -> int:

@@ -14,6 +14,10 @@ constexpr unsigned FULL = 0xFFFFFFFFu;
 // ---- launch accounting (pim_snappy_launch_count) ---------------------------
 void note_launch(unsigned n = 1);
 
+// ---- largest block size the COMPRESSOR accepts: PIM_SNAPPY_MAX_BLOCK_SIZE, or PIM_SNAPPY_MAX_EXTENDED_BLOCK_SIZE after
+// pim_snappy_set_extended_blocks(1) (the decoder never goes beyond the former)
+uint32_t max_compress_block_size();
+
 // ---- optional per-kernel event timing (pim_snappy_profile) ------------------
 // which: 0 compress, 1 scan, 2 compact, 3 decompress.  No-ops unless profiling is enabled.
 void prof_begin(int which, cudaStream_t st);

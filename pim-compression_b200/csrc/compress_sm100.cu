@@ -280,7 +280,7 @@ snappy_status pimsnappy::compress_batch_placed(int n_streams, const uint8_t *con
                                                uint8_t *const *d_scratch, const uint64_t *scratch_bytes, uint8_t *const *d_out,
                                                uint64_t *const *d_block_off, cudaStream_t st, bool alone_on_gpu)
 {
-	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE)
+	if (block_size == 0 || block_size > max_compress_block_size())
 		return SNAPPY_BUFFER_TOO_SMALL;
 	if (n_streams < 0 || n_streams > (int)MAX_BATCH)
 		return SNAPPY_INVALID_INPUT;

@@ -303,7 +303,7 @@ PW_FN void walk_serial(const CBlock &c, Walk &w, bool has_ic, bool valid, uint32
 		const int want = eff ? 31 - wp::clz32(eff) : -1;
 		if (want != loaded && valid) {
 			loaded = want;
-			cand = want < 0 ? tc : p - lane + want;
+			cand = want < 0 ? tc : (p - lane + want) & 0xFFFFu; // (what the table would hold: entries are 16 bits wide, :139)
 			mlen = common_prefix16(c, cand, cur);
 		}
 		const uint32_t hits = wp::ballot(valid && lane >= cont && mlen >= 4);
@@ -350,7 +350,7 @@ PW_FN void walk_serial(const CBlock &c, Walk &w, bool has_ic, bool valid, uint32
 constexpr uint32_t CW_RING = PIM_CW_RING; // records in flight between the two warps
 
 struct EmitRec {
-	uint32_t lanew[32]; // per lane: first byte at its position | match length << 8 | copy offset << 16
+	uint32_t lanew[32]; // per lane: first byte at its position | (match length - 4) << 8 (4 bits) | copy offset << 12 (20 bits: blocks up to 1 MiB)
 	uint32_t L;         // in-window literal bytes
 	uint32_t H;         // hit lanes
 	uint32_t V;         // insert lanes
@@ -473,7 +473,7 @@ PW_FN uint32_t emit_block_warp(const CBlock &c, EmitRing *ring, uint32_t &tail)
 		const uint32_t LS = L & (V << 1); // first byte of each in-window literal
 		const uint32_t Hb = H & ~satbit;  // hit lanes whose tag is written here
 		if (L | Hb) {
-			const uint32_t mlen = (lanew >> 8) & 0xFFu, off = lanew >> 16;
+			const uint32_t mlen = 4u + ((lanew >> 8) & 15u), off = lanew >> 12;
 			const bool inHb = (Hb >> lane) & 1u;
 			const bool three = inHb && !(mlen < 12 && off < 2048);
 			const uint32_t H3 = wp::ballot(three);
@@ -567,7 +567,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 			wp::syncwarp(); // every lane has read its slot before anyone writes
 			// Speculative insert + read-back: a lane that does not read its own position back shares
 			// its slot with another lane of this pass.
-			uint32_t w1 = p;
+			uint32_t w1 = p & 0xFFFFu;
 			uint32_t same = mybit, lowmask = 0, dup1;
 			bool involved;
 			if (GT && PIM_GT_MATCH) {
@@ -591,20 +591,20 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				wp::syncwarp();
 				if (valid)
 					w1 = wp::tbl_ld<GT>(c.table, h);
-				dup1 = wp::ballot(w1 != p);
+				dup1 = wp::ballot(w1 != (p & 0xFFFFu)); // (table entries are 16 bits wide, snappy_compress.c:139: above 64 KB the position comes back truncated)
 				involved = false;
 			}
 			const uint32_t inval = wp::ballot(!valid);
 			if (dup1) { // some lanes share a slot: find the groups (a second round tells the winners)
 				CW_STAT(6);
 				if (!(GT && PIM_GT_MATCH)) {
-					uint32_t w2 = p;
-					if (valid && w1 != p)
+					uint32_t w2 = p & 0xFFFFu;
+					if (valid && w1 != (p & 0xFFFFu))
 						wp::tbl_st<GT>(c.table, h, p);
 					wp::syncwarp();
 					if (valid)
 						w2 = wp::tbl_ld<GT>(c.table, h);
-					involved = valid && (w1 != p || w2 != p);
+					involved = valid && (w1 != (p & 0xFFFFu) || w2 != (p & 0xFFFFu));
 					same = wp::match_any(involved ? h : 0xFFFFFFFFu);
 				}
 				if (!involved)
@@ -613,7 +613,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				const int src = lowmask ? 31 - wp::clz32(lowmask) : lane;
 				const uint32_t pfwd = wp::shfl(p, src);
 				if (lowmask) { // the closest lower lane with my hash is my candidate (if it is really inserted)
-					cand = pfwd;
+					cand = pfwd & 0xFFFFu; // (the value the reference would read back from its 16-bit table)
 					mlen = common_prefix16(c, cand, cur);
 				}
 			}
@@ -696,7 +696,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				emit = q;
 			}
 			if (L | w.H | lit_len)
-				ring_push(ring, head, (cur[0] & 0xFFu) | (mlen << 8) | ((p - cand) << 16), L, w.H, w.V, w.satbit, lit_from, lit_len, copy_off,
+				ring_push(ring, head, (cur[0] & 0xFFu) | (((mlen - 4u) & 15u) << 8) | ((p - cand) << 12), L, w.H, w.V, w.satbit, lit_from, lit_len, copy_off,
 				          copy_len, 0u, lane);
 			wp::syncwarp(); // table writes visible to the next pass
 

@@ -26,6 +26,18 @@
 namespace pimsnappy {
 
 static std::atomic<uint64_t> g_launches{0};
+static std::atomic<int> g_extended{-1}; // -1: not set yet ($PIM_SNAPPY_EXTENDED_BLOCKS), 0 / 1
+uint32_t max_compress_block_size()
+{
+	int v = g_extended.load(std::memory_order_relaxed);
+	if (v < 0) {
+		const char *e = getenv("PIM_SNAPPY_EXTENDED_BLOCKS");
+		v = e && atoi(e) != 0 ? 1 : 0;
+		g_extended.store(v);
+	}
+	return v ? PIM_SNAPPY_MAX_EXTENDED_BLOCK_SIZE : PIM_SNAPPY_MAX_BLOCK_SIZE;
+}
+
 void note_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // ---- per-kernel event timing --------------------------------------------------
@@ -790,7 +802,7 @@ extern "C" snappy_status snappy_compress_gpu(struct host_buffer_context *input, 
 	std::lock_guard<std::mutex> api(g_api_mu);
 	double t0 = now_s();
 	runtime->d_alloc = runtime->load = runtime->copy_in = runtime->run = runtime->copy_out = runtime->d_free = 0;
-	if (block_size == 0 || block_size > PIM_SNAPPY_MAX_BLOCK_SIZE) {
+	if (block_size == 0 || block_size > max_compress_block_size()) {
 		fprintf(stderr, "pim_snappy: block size %u is outside the format's valid domain (1..%u)\n", block_size, PIM_SNAPPY_MAX_BLOCK_SIZE);
 		return SNAPPY_BUFFER_TOO_SMALL;
 	}
@@ -1073,6 +1085,7 @@ extern "C" snappy_status snappy_decompress_gpu(struct host_buffer_context *input
 }
 
 extern "C" void pim_snappy_set_write_file(int enable) { g_write_file.store(enable ? 1 : 0); }
+extern "C" void pim_snappy_set_extended_blocks(int enable) { g_extended.store(enable ? 1 : 0); }
 
 // The reference's names.  Its DPU compressor writes output->file_name itself (snappy_compress.c:626-627,697-703) and its
 // main() then skips write_output_host (dpu_snappy.c:209); with pim_snappy_set_write_file(1) / $PIM_SNAPPY_WRITE_FILE=1

@@ -112,3 +112,20 @@ def test_global_table_variant(emu, oracle, golden):
         assert st[6] > 0  # shared-slot passes occurred
     finally:
         emu.set_global_table(False)
+
+
+def test_extended_blocks_reproduce_the_references_truncations(emu, oracle, golden):
+    """above 65,536 bytes per block the reference's 16-bit table entries and copy offsets
+    (snappy_compress.c:139,241-243,347) make it emit streams that do not decode; the warp compressor must emit the same
+    bytes (the oracle restatement is pinned to the reference itself for these sizes in tests/test_oracle.py)."""
+    txt = golden["world192"][0]
+    rng = np.random.default_rng(5)
+    low = rng.integers(0, 4, 300000, dtype=np.uint8)
+    for gt in (False, True):
+        emu.set_global_table(gt)
+        for order in (0, 2):
+            emu.set_order(order)
+            for data, bs in ((txt, 131072), (txt[:700000], 1048576), (low, 262144), (txt[:200000], 65537)):
+                assert _same(emu.compress(data, bs), oracle.compress(data, bs)), (bs, gt, order)
+    emu.set_global_table(False)
+    emu.set_order(0)

@@ -413,3 +413,30 @@ def test_periodic_runs(P, oracle):
     data = np.concatenate(parts)
     for bs in (32768, 65536, 4096, 1000):
         _roundtrip_check(P, oracle, f"periodic/{bs}", data, bs, ref_decoder_ok=bs < 65536)
+
+
+def test_extended_domain_compressor(P, oracle, golden):
+    """SURVEY 8(f) N4 / BASELINE config 3 "sweep to 1 MB": off by default; when switched on the compressor gives the
+    reference's bytes above 65,536 bytes per block (streams that do not decode in the reference either), the decoder
+    still refuses them."""
+    data = np.concatenate([golden["world192"][0], P.synth_host(P.SYNTH_BIN, 0x0B1A, 3 << 20), P.synth_host(P.SYNTH_TEXT, 0x5BA0, 2 << 20)])
+    with pytest.raises(P.SnappyError) as e:
+        P.compress(data, 131072)
+    assert e.value.status == P.SNAPPY_BUFFER_TOO_SMALL
+    P.set_extended_blocks(True)
+    try:
+        for bs in (65537, 131072, 262144, 1048576, 1000000):
+            want = oracle.compress(data, bs)
+            for chunk in (0, 2 << 20):
+                P.set_chunk_bytes(chunk)
+                got = P.compress(data, bs)
+                assert got.size == want.size and np.array_equal(got, want), (bs, chunk)
+        with pytest.raises(P.SnappyError) as e:
+            P.decompress(want)
+        assert e.value.status == P.SNAPPY_BUFFER_TOO_SMALL
+        with pytest.raises(P.SnappyError):
+            P.compress(data, 1048577)
+        assert np.array_equal(P.compress(data, 65536), oracle.compress(data, 65536))  # the valid domain is unchanged
+    finally:
+        P.set_extended_blocks(False)
+        P.set_chunk_bytes(32 << 20)

@@ -105,3 +105,13 @@ def test_against_reference_sweep(golden, oracle, P):
             if bs <= 65535:
                 rc, out = ref.decompress(a)
                 assert rc == 0 and np.array_equal(out, data), (name, bs)
+
+
+def test_against_reference_above_64k(golden, oracle, P):
+    """Extended domain: the restatement reproduces the reference's bytes -- 16-bit truncations
+    included -- for block sizes up to 1 MiB, so it can be the checker for the GPU compressor's extended mode."""
+    ref = _ref()
+    inputs = {"world192": golden["world192"][0], "bin": P.synth_host(P.SYNTH_BIN, 6, 700000), "text": P.synth_host(P.SYNTH_TEXT, 5, 600000)}
+    for name, data in inputs.items():
+        for bs in (65537, 131072, 262144, 1048576):
+            assert np.array_equal(oracle.compress(data, bs), ref.compress(data, bs)), (name, bs)
