@@ -390,11 +390,11 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t pari
 	asm volatile("{\n"
 	             ".reg .pred p;\n"
 	             "LAB_WAIT:\n"
-	             "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	             "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n" // (with a suspend-time hint: without one the wait comes back every few hundred cycles)
 	             "@p bra LAB_DONE;\n"
 	             "bra LAB_WAIT;\n"
 	             "LAB_DONE:\n"
-	             "}" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+	             "}" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity), "r"(0x989680u) : "memory");
 }
 PW_FN void ring_init(EmitRing *ring) // by one thread, before the pair's first barrier
 {
