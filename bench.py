@@ -429,19 +429,27 @@ def run_ours(args):
                 t0 = time.perf_counter()
                 clen = e2e_stream(0)
                 return clen, time.perf_counter() - t0
-            assert P.set_devices(list(range(world))) == world
-            one_stream()
-            times = []
-            for _ in range(3):
-                clen_n, dt1 = one_stream()
-                times.append(dt1)
-            comp_n = h_comp.array[:clen_n].copy()
-            back_ok = bool(np.array_equal(h_back.array[:n], h_in[0].array))
-            assert P.set_devices([local_rank]) == 1
-            clen_1, _ = one_stream()
-            e2e_sharded = {"value": n / min(times) / 1e9, "unit": "GB/s", "n_gpus": world, "stream_bytes": n,
-                           "bytes_equal_to_1gpu": bool(clen_1 == clen_n and np.array_equal(h_comp.array[:clen_1], comp_n)) and back_ok,
-                           "api": "snappy_compress_dpu + snappy_decompress_dpu on ONE stream with pim_snappy_set_devices([0..N-1]), best of 3"}
+            try:  # (never let this extra leg take the headline run down; the other ranks wait at the barrier below)
+                seen = P.set_devices(list(range(world)))
+                if seen != world:
+                    e2e_sharded = {"skipped": f"rank 0 sees {seen} of {world} GPUs"}
+                else:
+                    one_stream()
+                    times = []
+                    for _ in range(3):
+                        clen_n, dt1 = one_stream()
+                        times.append(dt1)
+                    comp_n = h_comp.array[:clen_n].copy()
+                    back_ok = bool(np.array_equal(h_back.array[:n], h_in[0].array))
+                    assert P.set_devices([local_rank]) == 1
+                    clen_1, _ = one_stream()
+                    e2e_sharded = {"value": n / min(times) / 1e9, "unit": "GB/s", "n_gpus": world, "stream_bytes": n,
+                                   "bytes_equal_to_1gpu": bool(clen_1 == clen_n and np.array_equal(h_comp.array[:clen_1], comp_n)) and back_ok,
+                                   "api": "snappy_compress_dpu + snappy_decompress_dpu on ONE stream with pim_snappy_set_devices([0..N-1]), best of 3"}
+            except Exception as ex:  # noqa: BLE001
+                e2e_sharded = {"error": repr(ex)[:300]}
+            finally:
+                P.set_devices([local_rank])
         sync_all()
 
     # ---- the same two kernels on other inputs (one 1-stream launch each, after one warm launch): text, the reference's
