@@ -468,6 +468,7 @@ def run_ours(args):
                  "SYN-BIN": lambda: P.synth_device(P.SYNTH_BIN, 0x0B1A, d_in[0].data_ptr(), n, st)}
         by_input = {}
         for name, fill in fills.items():
+          try:  # (an extra leg: a failure is recorded, it does not take the headline run down)
             fill()
             torch.cuda.synchronize()
             P.profile(True)
@@ -486,6 +487,9 @@ def run_ours(args):
                 row[k] = {"ms": ms, "uncompressed_gbps": n / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": (n + cb) / (ms * 1e-3) / 1e9 / peak}
             row["compress"]["scan_compact_ms"] = pr["scan"]["ms"] + pr["compact"]["ms"]
             by_input[name] = row
+          except Exception as ex:  # noqa: BLE001
+            P.profile(False)
+            by_input[name] = {"error": repr(ex)[:300]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -121,11 +121,10 @@ def test_extended_blocks_reproduce_the_references_truncations(emu, oracle, golde
     txt = golden["world192"][0]
     rng = np.random.default_rng(5)
     low = rng.integers(0, 4, 300000, dtype=np.uint8)
-    for gt in (False, True):
+    for gt, order in ((False, 0), (True, 2)):
         emu.set_global_table(gt)
-        for order in (0, 2):
-            emu.set_order(order)
-            for data, bs in ((txt, 131072), (txt[:700000], 1048576), (low, 262144), (txt[:200000], 65537)):
-                assert _same(emu.compress(data, bs), oracle.compress(data, bs)), (bs, gt, order)
+        emu.set_order(order)
+        for data, bs in ((txt[:500000], 131072), (txt[:700000], 1048576), (low, 262144), (txt[:200000], 65537)):
+            assert _same(emu.compress(data, bs), oracle.compress(data, bs)), (bs, gt, order)
     emu.set_global_table(False)
     emu.set_order(0)
