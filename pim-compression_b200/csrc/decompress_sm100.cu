@@ -639,9 +639,8 @@ __device__ __forceinline__ void decode_block(Dec &d)
 }
 
 // ---------------------------------------------------------------------------
-// Kernel: persistent CTAs of WARPS independent warps; every warp pulls the next block of the concatenation of
-// the batch's streams' blocks from a counter (one launch decodes up to DEC_MAX_BATCH streams,
-// pim_snappy_decompress_batch_device, so that no SM idles between streams).
+// Kernel: persistent CTAs of WARPS independent warps over the concatenation of the batch's streams' blocks (one launch
+// decodes up to DEC_MAX_BATCH streams, pim_snappy_decompress_batch_device, so that no SM idles between streams).
 // ---------------------------------------------------------------------------
 constexpr uint32_t DEC_MAX_BATCH = 32;
 struct DecStream {
@@ -660,6 +659,20 @@ struct DecArgs {
 	unsigned long long *counter; // next block of the batch (zero at launch)
 };
 
+#ifndef PIM_DEC_QUEUE
+#define PIM_DEC_QUEUE 0 // block order of the kernel below: 0 fixed stride, 2 stride + counter for the tail
+#endif
+#if PIM_DEC_QUEUE != 0
+// the next index of the block counter, for the whole warp
+__device__ __noinline__ unsigned long long pull_block(unsigned long long *counter)
+{
+	unsigned long long g = 0;
+	if (lane_id() == 0)
+		g = atomicAdd(counter, 1ull);
+	return __shfl_sync(FULL, g, 0);
+}
+#endif
+
 __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_kernel(const __grid_constant__ DecArgs a)
 {
 	extern __shared__ __align__(16) uint8_t sm[];
@@ -677,31 +690,23 @@ __global__ void __launch_bounds__(32 * WARPS, PIM_DEC_MINB) snappy_decompress_ke
 	d.sm = sm;
 	d.ws = sm + SM_WARP0 + warp * WS_BYTES;
 	d.lane = lane;
-	// every warp pulls the next block of the batch (the reference hands each tasklet a fixed contiguous run,
-	// dpu-decompress/dpu_task.c:42-77; with a queue a warp that drew slow blocks does not set the tail)
-	// Block order: all but the last full round of blocks go to the warps by a fixed stride, what is left after that is
-	// pulled from a counter, so that a warp that drew slow blocks does not set the tail (the reference hands each tasklet
-	// a fixed contiguous run, dpu-decompress/dpu_task.c:42-77).  Measured on B200 (1 GiB, GB/s text / mix / corpus / bin):
-	// stride only 213 / 352 / 147 / 491, counter only 191 / 317 / 152 / 427.
-#ifndef PIM_DEC_QUEUE
-#define PIM_DEC_QUEUE 2 // 0: stride only, 1: counter only, 2: stride, then the counter for the last rounds
+	// Block order.  Default (PIM_DEC_QUEUE 0): warp g of the grid decodes blocks g, g + warps, ... of the batch.
+	// PIM_DEC_QUEUE 2: all but the last full round that way, the rest pulled from a counter in global memory, so that a
+	// warp that drew slow blocks does not set the tail (the reference hands each tasklet a fixed contiguous run,
+	// dpu-decompress/dpu_task.c:42-77).  Measured on B200 in round 2 (profiles/r2_decoder_experiments.md): every loop
+	// shape that contains the counter makes the compiler lay the decoder out differently (12,100 instead of 9,900 SASS
+	// lines, twice the local-memory accesses) and costs 5-15 % on uniform data (SYN-MIX 320-357 vs 375 GB/s, text 191 vs
+	// 213) for 3 % on the tiled fixtures (152 vs 147), so the plain stride stays the default.
+	const uint64_t total_warps = (uint64_t)gridDim.x * WARPS;
+#if PIM_DEC_QUEUE == 0
+	for (uint64_t gblk = (uint64_t)blockIdx.x * WARPS + warp; gblk < a.nblocks; gblk += total_warps) {
+#else
+	const uint64_t rounds = a.nblocks / total_warps;
+	const uint64_t static_rounds = rounds > 1 ? rounds - 1 : 1;
+	uint64_t done = 0; // rounds this warp has finished
+	for (uint64_t gblk = (uint64_t)blockIdx.x * WARPS + warp; gblk < a.nblocks;
+	     gblk = ++done < static_rounds ? gblk + total_warps : static_rounds * total_warps + pull_block(a.counter)) {
 #endif
-	const unsigned long long total_warps = (unsigned long long)gridDim.x * WARPS;
-	const unsigned long long wid = (unsigned long long)blockIdx.x * WARPS + warp;
-	const unsigned long long rounds = a.nblocks / total_warps;
-	const unsigned long long static_rounds = PIM_DEC_QUEUE == 0 ? ~0ull : (PIM_DEC_QUEUE == 1 ? 0ull : (rounds > 1 ? rounds - 1 : 0ull));
-	for (unsigned long long r = 0;; r++) {
-		unsigned long long gblk;
-		if (r < static_rounds) {
-			gblk = r * total_warps + wid;
-		} else {
-			gblk = 0;
-			if (lane == 0)
-				gblk = static_rounds * total_warps + atomicAdd(a.counter, 1ull);
-			gblk = __shfl_sync(FULL, gblk, 0);
-		}
-		if (gblk >= a.nblocks)
-			break;
 		uint32_t si = 0;
 		while (si + 1 < a.n_streams && gblk >= a.s[si + 1].first_blk)
 			si++;
@@ -772,18 +777,19 @@ extern "C" snappy_status pim_snappy_decompress_batch_device(int n_streams, const
 	{
 		std::lock_guard<std::mutex> lk(g_dec_mu);
 		DecDevice &dd = g_dec[dev];
-		if (!dd.counters) {
+		if (!dd.max_ctas) {
 			PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
 			PIM_CUDA_TRY(cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
 			int per_sm = 0, sms = 0;
 			PIM_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, snappy_decompress_kernel, 32 * WARPS, SMEM_BYTES));
 			PIM_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 			dd.max_ctas = per_sm * sms > 0 ? per_sm * sms : 1;
-			PIM_CUDA_TRY(cudaMalloc(&dd.counters, sizeof(unsigned long long) * POOL));
+			if (PIM_DEC_QUEUE != 0)
+				PIM_CUDA_TRY(cudaMalloc(&dd.counters, sizeof(unsigned long long) * POOL));
 		}
 		if (dd.next + launches > (unsigned)POOL)
 			dd.next = 0;
-		counters = dd.counters + dd.next;
+		counters = dd.counters ? dd.counters + dd.next : nullptr;
 		dd.next += launches;
 		max_ctas = dd.max_ctas;
 	}
@@ -807,8 +813,10 @@ extern "C" snappy_status pim_snappy_decompress_batch_device(int n_streams, const
 		if (total == 0)
 			continue;
 		da.nblocks = total;
-		da.counter = counters + launch_i++;
-		PIM_CUDA_TRY(cudaMemsetAsync(da.counter, 0, sizeof(unsigned long long), st));
+		if (counters) {
+			da.counter = counters + launch_i++;
+			PIM_CUDA_TRY(cudaMemsetAsync(da.counter, 0, sizeof(unsigned long long), st));
+		}
 		const uint64_t want = (total + WARPS - 1) / WARPS;
 		const unsigned grid = (unsigned)(want < (uint64_t)max_ctas ? want : (uint64_t)max_ctas);
 		prof_begin(3, st);
