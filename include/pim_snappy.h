@@ -167,6 +167,19 @@ snappy_status pim_snappy_compress_device(const uint8_t *d_in, uint64_t input_len
                                          uint8_t *d_scratch, uint64_t scratch_bytes,
                                          uint8_t *d_out, uint64_t *d_block_off, void *stream);
 
+/* pim_snappy_compress_device() for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same inputs,
+ * outputs and bytes as pim_snappy_compress_device(); the scratch is a device array built into the library
+ * (PIM_SNAPPY_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library until exit), so the call makes no
+ * cudaMalloc / cudaFree or any other allocation.  Inputs whose pim_snappy_compress_scratch_bytes() exceeds the array
+ * (about 18 MiB of input at 32 KiB blocks: 42 MB of the array are hash tables) are rejected with
+ * SNAPPY_BUFFER_TOO_SMALL and a message.  All calls on one GPU share the array: it keeps the last call's contents
+ * (every call clears what must start at zero), and calls that OVERLAP on the GPU -- different streams, or several host
+ * threads -- race; serialise them, or use pim_snappy_compress_device() with scratch of your own. */
+#define PIM_SNAPPY_NOALLOC_SCRATCH_BYTES (64u << 20)
+snappy_status pim_snappy_compress_device_noalloc(const uint8_t *d_in, uint64_t input_len, uint32_t block_size,
+                                                 uint8_t *d_out, uint64_t *d_block_off, void *stream);
+
 /* Decompress nblocks blocks.  d_block_off[0..nblocks] as produced above (or by
  * the host header walk): block i occupies d_comp[d_block_off[i] ..
  * d_block_off[i+1]) = 4-byte size + elements.  Block i decodes to exactly

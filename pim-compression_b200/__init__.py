@@ -26,6 +26,7 @@ from .api import (  # noqa: F401
     compress,
     decompress,
     compress_device,
+    compress_device_noalloc,
     compress_batch_device,
     decompress_batch_device,
     decompress_device,

@@ -80,6 +80,7 @@ def lib() -> C.CDLL:
         "pim_snappy_compress_bound": (C.c_uint64, [C.c_uint64, C.c_uint32]),
         "pim_snappy_compress_scratch_bytes": (C.c_uint64, [C.c_uint64, C.c_uint32]),
         "pim_snappy_compress_device": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
+        "pim_snappy_compress_device_noalloc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
         "pim_snappy_decompress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
         "pim_snappy_compress_batch_device": (C.c_int, [C.c_int, P(C.c_void_p), P(C.c_uint64), C.c_uint32, P(C.c_void_p), P(C.c_uint64), P(C.c_void_p),
                                                        P(C.c_void_p), C.c_void_p]),
@@ -104,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "setup_compression", "setup_decompression", "snappy_compress_dpu", "snappy_decompress_dpu",
     "snappy_compress_gpu", "snappy_decompress_gpu", "get_runtime", "pim_snappy_host_alloc", "pim_snappy_host_free",
     "pim_snappy_set_devices", "pim_snappy_device_count", "pim_snappy_set_chunk_bytes", "pim_snappy_set_write_file", "pim_snappy_set_extended_blocks", "pim_snappy_shard_range", "pim_snappy_num_blocks", "pim_snappy_compress_bound",
-    "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_decompress_device", "pim_snappy_compress_batch_device",
+    "pim_snappy_compress_scratch_bytes", "pim_snappy_compress_device", "pim_snappy_compress_device_noalloc", "pim_snappy_decompress_device", "pim_snappy_compress_batch_device",
     "pim_snappy_decompress_batch_device", "pim_snappy_gather_shards",
     "pim_snappy_launch_count", "pim_snappy_profile", "pim_snappy_profile_read", "pim_snappy_version",
 ]
@@ -264,6 +265,16 @@ def compress_device(d_in_ptr: int, n: int, block_size: int, d_scratch_ptr: int, 
     st = lib().pim_snappy_compress_device(d_in_ptr, n, block_size, d_scratch_ptr, scratch_bytes, d_out_ptr, d_off_ptr, stream)
     if st != SNAPPY_OK:
         raise SnappyError(st, "pim_snappy_compress_device")
+
+
+NOALLOC_SCRATCH_BYTES = 64 << 20  # PIM_SNAPPY_NOALLOC_SCRATCH_BYTES
+
+
+def compress_device_noalloc(d_in_ptr: int, n: int, block_size: int, d_out_ptr: int, d_off_ptr: int, stream: int = 0) -> None:
+    """pim_snappy_compress_device_noalloc: scratch in the library's built-in device array, no allocation in the call."""
+    st = lib().pim_snappy_compress_device_noalloc(d_in_ptr, n, block_size, d_out_ptr, d_off_ptr, stream)
+    if st != SNAPPY_OK:
+        raise SnappyError(st, "pim_snappy_compress_device_noalloc")
 
 
 def compress_batch_device(d_in_ptrs, lens, block_size: int, d_scratch_ptrs, scratch_bytes, d_out_ptrs, d_off_ptrs, stream: int = 0) -> None:

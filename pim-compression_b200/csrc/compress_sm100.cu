@@ -26,6 +26,8 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "compress_warp.cuh"
 
@@ -273,6 +275,52 @@ extern "C" snappy_status pim_snappy_compress_batch_device(int n_streams, const u
 			return r;
 	}
 	return SNAPPY_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// pim_snappy_compress_device_noalloc: pim_snappy_compress_device() with its scratch in a file-scope device array, for
+// callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No
+// counterpart in the reference.
+//
+// Every GPU that loads the library holds the array (PIM_SNAPPY_NOALLOC_SCRATCH_BYTES) until exit.  In host code the
+// array's name is only a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress, once per
+// device with that device current.  All calls on a device share the array: calls that overlap on the GPU race.  What
+// must start at zero is cleared by every call (the block counter: cudaMemsetAsync in compress_batch_placed; the hash
+// tables: zeroed per block by the kernel, get_hash_table snappy_compress.c:139-146); sizes and slots are written before
+// they are read.  Calls no cudaMalloc / cudaFree / allocating routine.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) uint8_t g_noalloc_scratch[PIM_SNAPPY_NOALLOC_SCRATCH_BYTES];
+
+extern "C" snappy_status pim_snappy_compress_device_noalloc(const uint8_t *d_in, uint64_t input_len, uint32_t block_size, uint8_t *d_out,
+                                                            uint64_t *d_block_off, void *stream)
+{
+	if (block_size == 0 || block_size > max_compress_block_size())
+		return SNAPPY_BUFFER_TOO_SMALL;
+	const uint64_t need = pim_snappy_compress_scratch_bytes(input_len, block_size);
+	if (need > (uint64_t)PIM_SNAPPY_NOALLOC_SCRATCH_BYTES) {
+		fprintf(stderr, "pim_snappy_compress_device_noalloc: %llu input bytes at block size %u need %llu bytes of scratch, the built-in array holds %llu; "
+		                "use pim_snappy_compress_device with scratch of your own\n",
+		        (unsigned long long)input_len, block_size, (unsigned long long)need, (unsigned long long)PIM_SNAPPY_NOALLOC_SCRATCH_BYTES);
+		return SNAPPY_BUFFER_TOO_SMALL;
+	}
+	static std::mutex mu;
+	static uint8_t *scratch_addr[64] = {nullptr}; // per device: the array's device address
+	int dev = 0;
+	PIM_CUDA_TRY(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= 64)
+		return SNAPPY_INVALID_INPUT;
+	uint8_t *scratch = nullptr;
+	{
+		std::lock_guard<std::mutex> lk(mu);
+		if (!scratch_addr[dev]) {
+			void *p = nullptr;
+			PIM_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch)); // (the current device's copy of the array)
+			scratch_addr[dev] = static_cast<uint8_t *>(p);
+		}
+		scratch = scratch_addr[dev];
+	}
+	return compress_device_placed(d_in, input_len, block_size, scratch, PIM_SNAPPY_NOALLOC_SCRATCH_BYTES, d_out, d_block_off,
+	                              static_cast<cudaStream_t>(stream), true);
 }
 
 // Streams [0, n_streams) (n_streams <= MAX_BATCH) in ONE compress launch, then one size scan + compaction per stream.
