@@ -240,47 +240,59 @@ struct Walk {
 };
 
 // Fast walk: every lane's candidate is fixed (table entry, or the closest lower lane with the same
-// hash); one warp reduction per pair fetches the hit lane's "next insert lane".
+// hash).  The reference's loop (:370-398) goes hit -> end of its match -> next hit -> ...; here every lane works out, in
+// parallel and once per pass, where the chain would go after a hit at ITS position (the next hit lane at or above its
+// continuation lane, its insert lane, whether the pass may continue there), and the chain is then followed with one
+// shuffle per pair.  (Round 1 fetched the hit lane's data with a warp reduction and re-derived the rest per pair: 27 % of
+// the kernel's instructions.)
 PW_FN void walk_fast(Walk &w, bool has_ic, bool dense, uint32_t hits, uint32_t inval, uint32_t mynins, uint32_t mybit)
 {
+	(void)mybit;
+	const bool sat = mynins == CW_SAT;
+	const uint32_t nv = sat ? 0u : mynins; // my match's insert lane (:388-389), 0 if I am no hit or it lies beyond the window
+	// continue in this pass after my match if the next pair's insert lane and continuation lane are usable
+	const bool cont = dense && nv != 0u && nv <= (1u << CW_CHAIN_MAX) && ((nv << 1) & ~inval);
+	const uint32_t after = hits & (0u - (nv << 1)); // hit lanes at or above my continuation lane
+	const uint32_t word = (after ? (uint32_t)wp::ffs32(after) - 1u : 32u) | ((nv ? 31u - (uint32_t)wp::clz32(nv) : 0u) << 8) | (cont ? 1u << 16 : 0u) |
+	                      (sat ? 1u << 17 : 0u);
 	w.V = has_ic ? 1u : 0u;
 	w.H = w.firstbit = w.lastbit = w.satbit = 0;
 	w.insbit = w.V;
 	w.first = true;
 	w.redo = false;
-	uint32_t above = has_ic ? ~1u : ~0u; // lanes that may hit in the current pair
+	const uint32_t ab = hits & (has_ic ? ~1u : ~0u);
+	if (!ab) { // inval: :341 / :386, the rest of the block is one literal; otherwise keep probing
+		w.outcome = inval ? 2 : 1;
+		return;
+	}
+	uint32_t cur = (uint32_t)wp::ffs32(ab) - 1u;
+	w.firstbit = 1u << cur;
 	for (;;) {
-		const uint32_t ab = hits & above;
-		if (!ab) {
-			// inval: :341 / :386, the rest of the block is one literal.  Otherwise the window is
-			// exhausted: a first pair keeps probing, a later pair is redone with a window of its own.
-			w.outcome = inval ? 2 : (w.first ? 1 : 0);
-			w.redo = !inval && !w.first;
-			return;
-		}
 		CW_STAT(2);
-		const uint32_t fbit = ab & (0u - ab);
-		const uint32_t nv = wp::reduce_max(mybit == fbit ? mynins : 0u);
+		const uint32_t x = wp::shfl(word, (int)cur);
+		const uint32_t fbit = 1u << cur;
 		w.H |= fbit;
 		w.lastbit = fbit;
-		if (w.first)
-			w.firstbit = fbit;
-		if (nv == CW_SAT) {
+		if (x & (1u << 17)) {
 			CW_STAT(4);
 			w.satbit = fbit;
 			w.outcome = 3;
 			return;
 		}
-		// continue in this pass if the next pair's insert lane and continuation lane are usable
-		const bool go = dense && nv != 0u && nv <= (1u << CW_CHAIN_MAX) && ((nv << 1) & ~inval);
-		if (!go) {
+		if (!(x & (1u << 16))) {
 			w.outcome = 0;
 			return;
 		}
-		w.V |= nv;
-		w.insbit = nv;
-		above = 0u - (nv << 1);
+		const uint32_t nvb = 1u << ((x >> 8) & 31u);
+		w.V |= nvb;
+		w.insbit = nvb;
 		w.first = false;
+		cur = x & 0xFFu;
+		if (cur == 32u) { // the window is exhausted: the pair gets a pass of its own (or the block ends, inval)
+			w.outcome = inval ? 2 : 0;
+			w.redo = !inval;
+			return;
+		}
 	}
 }
 
