@@ -29,6 +29,9 @@
 #include <mutex>
 
 #include "common.cuh"
+#ifdef PIM_CW_PROFILE
+namespace pimsnappy { __device__ unsigned long long g_cw_prof[16]; }
+#endif
 #include "compress_warp.cuh"
 
 namespace pimsnappy {
@@ -230,6 +233,20 @@ __global__ void __launch_bounds__(128) compact_kernel(const uint8_t *__restrict_
 
 } // namespace
 } // namespace pimsnappy
+
+#ifdef PIM_CW_PROFILE // development aid: see compress_warp.cuh
+extern "C" int pim_snappy_debug_cw_prof(unsigned long long out[16], int reset)
+{
+	if (cudaMemcpyFromSymbol(out, pimsnappy::g_cw_prof, sizeof(unsigned long long) * 16) != cudaSuccess)
+		return 1;
+	if (reset) {
+		unsigned long long z[16] = {0};
+		if (cudaMemcpyToSymbol(pimsnappy::g_cw_prof, z, sizeof(z)) != cudaSuccess)
+			return 1;
+	}
+	return 0;
+}
+#endif
 
 using namespace pimsnappy;
 

@@ -42,6 +42,23 @@ namespace pimsnappy { extern unsigned long cw_stats[8]; }
 #define CW_STAT(i) do { } while (0)
 #endif
 
+// Development aid (-DPIM_CW_PROFILE, device only): cycles of the parser's pass, by segment, summed over all passes of all
+// shared-memory-table pairs into g_cw_prof (read with pim_snappy_debug_cw_prof, compress_sm100.cu).
+#if defined(PIM_CW_PROFILE) && !defined(PIM_WARP_EMU)
+// (g_cw_prof is defined by the including .cu file before this header)
+#define CW_T_DECL long long cw_tprev = clock64(); unsigned long long cw_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long cw_passes = 0
+#define CW_T(i) do { const long long t__ = clock64(); cw_acc[i] += (unsigned long long)(t__ - cw_tprev); cw_tprev = t__; } while (0)
+#define CW_T_USE(v) do { if (wp::ballot((v) == 0x9E3779B9u) == 0xFFFFFFFFu) cw_passes += 1000000; } while (0) /* waits for v */
+#define CW_T_PASS do { cw_passes++; } while (0)
+#define CW_T_FLUSH do { if (!GT && wp::lane() == 0) { for (int i__ = 0; i__ < 8; i__++) atomicAdd(&pimsnappy::g_cw_prof[i__], cw_acc[i__]); atomicAdd(&pimsnappy::g_cw_prof[8], cw_passes); } } while (0)
+#else
+#define CW_T_DECL do { } while (0)
+#define CW_T(i) do { } while (0)
+#define CW_T_USE(v) do { } while (0)
+#define CW_T_PASS do { } while (0)
+#define CW_T_FLUSH do { } while (0)
+#endif
+
 namespace pimsnappy {
 
 constexpr uint32_t CW_MAX_TABLE = 16384; // snappy_compress.c:16-17
@@ -540,6 +557,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 	uint32_t emit = 0; // first input byte not yet emitted (next_emit)
 	uint32_t pf = 0;   // input below this position has been prefetched into L2
 
+	CW_T_DECL;
 	if (n >= CW_MARGIN) {
 		const uint32_t limit = n - CW_MARGIN;
 		uint32_t q = 1;      // ic layout: where the last match ended; probe layout: position of probe 0
@@ -549,6 +567,8 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 			if (has_ic && q >= limit) // :386
 				break;
 			CW_STAT(has_ic ? 0 : 1);
+			CW_T(7); // (loop control, between passes)
+			CW_T_PASS;
 			if (PIM_PF_AHEAD && pf < n && pf < q + PIM_PF_AHEAD) { // HBM -> L2 a few KB ahead of the parse (32 lines at a time)
 				const uint32_t at = pf + 128u * lane;
 				if (at < n + 24u)
@@ -571,11 +591,25 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 			// ---- per-lane probe --------------------------------------------------------------
 			uint32_t cur[4] = {0, 0, 0, 0};
 			uint32_t h = 0, tc = 0, cand = 0, mlen = 0;
+			CW_T(7);
+#if defined(PIM_CW_PROFILE) && !defined(PIM_WARP_EMU) // (the same probe with stamps between its steps; all lanes reach the votes)
+			if (valid) {
+				in_load128(c, p, cur);
+				h = (cur[0] * 0x1e35a7bdu) >> c.shift;
+			}
+			CW_T_USE(h);
+			CW_T(6); // own bytes arrived
+			if (valid)
+				tc = wp::tbl_ld<GT>(c.table, h);
+			CW_T_USE(tc);
+			CW_T(0); // table entry arrived
+#else
 			if (valid) {
 				in_load128(c, p, cur);
 				h = (cur[0] * 0x1e35a7bdu) >> c.shift; // :161-166
 				tc = wp::tbl_ld<GT>(c.table, h);
 			}
+#endif
 			wp::syncwarp(); // every lane has read its slot before anyone writes
 			// Speculative insert + read-back: a lane that does not read its own position back shares
 			// its slot with another lane of this pass.
@@ -607,6 +641,8 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				involved = false;
 			}
 			const uint32_t inval = wp::ballot(!valid);
+			CW_T_USE(mlen);
+			CW_T(1); // speculative insert + read-back, candidate bytes arrived, match lengths
 			if (dup1) { // some lanes share a slot: find the groups (a second round tells the winners)
 				CW_STAT(6);
 				if (!(GT && PIM_GT_MATCH)) {
@@ -631,6 +667,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 			}
 
 			// ---- resolve the pairs of this pass ------------------------------------------------
+			CW_T(2); // shared slots resolved
 			Walk w;
 			bool inI;       // my position is inserted into the table
 			uint32_t Imask;
@@ -659,6 +696,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 			}
 			if (w.redo)
 				CW_STAT(3);
+			CW_T(3); // the pair walk, forwarded candidates checked
 
 			// ---- table: undo the speculative inserts of lanes that were not inserted -----------
 			if (GT && PIM_GT_MATCH) { // (nothing was stored yet: the last inserted lane of every slot writes it)
@@ -674,6 +712,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				}
 			}
 
+			CW_T(4); // table updates
 			// ---- where the pass ended ----------------------------------------------------------
 			const bool by_ins = w.redo || (w.outcome == 2 && !w.first); // just past the last complete match
 			const bool have_pos = by_ins || w.outcome == 0 || w.outcome == 3;
@@ -684,6 +723,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				pos_last = wp::reduce_max(mybit == sel ? p + add : 0u);
 			}
 
+			CW_T(4); // position of the pass's end
 			// ---- hand the pass's output to the emitter warp -------------------------------------
 			uint32_t lit_from = 0, lit_len = 0, copy_off = 0, copy_len = 0;
 			if (!has_ic && w.firstbit) { // the first pair's literal started before this window
@@ -711,6 +751,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 				ring_push(ring, head, (cur[0] & 0xFFu) | (((mlen - 4u) & 15u) << 8) | ((p - cand) << 12), L, w.H, w.V, w.satbit, lit_from, lit_len, copy_off,
 				          copy_len, 0u, lane);
 			wp::syncwarp(); // table writes visible to the next pass
+			CW_T(5); // literal bounds, long matches, record to the emitter
 
 			if (outcome == 2)
 				break;
@@ -726,6 +767,7 @@ PW_FN void parse_block_warp(const CBlock &c, EmitRing *ring, uint32_t &head)
 			}
 		}
 	}
+	CW_T_FLUSH;
 	// the rest of the block is one literal (:405-409); this record also ends the block
 	ring_push(ring, head, 0u, 0u, 0u, 0u, 0u, emit, n - emit, 0u, 0u, 1u, lane);
 }
