@@ -60,9 +60,11 @@ struct program_runtime {
 double get_runtime(struct timeval *start, struct timeval *end);
 
 /* snappy/snappy_compress.h:16 (snappy_compress.c:418-453).  Allocates
- * output->buffer (page-locked, sized for the worst case INCLUDING the 4-byte
- * block headers the reference's bound forgets), output->curr = buffer,
- * output->length = 0, runtime->pre = elapsed. */
+ * output->buffer (sized for the worst case INCLUDING the 4-byte block headers
+ * the reference's bound forgets; page-locked when the call will be streamed,
+ * i.e. beyond two chunks, plain malloc below that -- release either with
+ * pim_snappy_host_free()), output->curr = buffer, output->length = 0,
+ * runtime->pre = elapsed. */
 void setup_compression(struct host_buffer_context *input, struct host_buffer_context *output,
                        struct program_runtime *runtime);
 

@@ -55,9 +55,10 @@ static int slurp(const char *path, struct host_buffer_context *in)
 		return 1;
 	}
 	in->length = (unsigned long)sz;
-	in->buffer = pim_snappy_host_alloc(((size_t)sz + 7) & ~(size_t)7);
+	/* page-locked memory pays for files the library streams (copies beside the kernels); locking a small buffer costs more than its copy */
+	in->buffer = sz > (64l << 20) ? pim_snappy_host_alloc(((size_t)sz + 7) & ~(size_t)7) : malloc((((size_t)sz + 7) & ~(size_t)7) + 8);
 	if (!in->buffer) {
-		fprintf(stderr, "cannot allocate page-locked memory (no CUDA device?)\n");
+		fprintf(stderr, "cannot allocate the input buffer (no CUDA device?)\n");
 		fclose(f);
 		return 1;
 	}

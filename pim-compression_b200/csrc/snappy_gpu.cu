@@ -88,7 +88,11 @@ double now_s()
 
 // ---- pinned host allocations made through pim_snappy_host_alloc -------------
 std::mutex g_alloc_mu;
-std::map<void *, size_t> g_allocs;
+struct HostAlloc {
+	size_t bytes;
+	bool pinned;
+};
+std::map<void *, HostAlloc> g_allocs;
 
 size_t owned_capacity(const void *p) // capacity from p to the end of our allocation, 0 if not ours
 {
@@ -99,9 +103,9 @@ size_t owned_capacity(const void *p) // capacity from p to the end of our alloca
 	--it;
 	const uint8_t *base = static_cast<const uint8_t *>(it->first);
 	const uint8_t *q = static_cast<const uint8_t *>(p);
-	if (q >= base + it->second)
+	if (q >= base + it->second.bytes)
 		return 0;
-	return it->second - (size_t)(q - base);
+	return it->second.bytes - (size_t)(q - base);
 }
 
 // ---- devices ----------------------------------------------------------------
@@ -673,7 +677,7 @@ extern "C" void *pim_snappy_host_alloc(size_t bytes)
 		return nullptr; // no pageable substitute: the caller sees the failure
 	}
 	std::lock_guard<std::mutex> lk(g_alloc_mu);
-	g_allocs[p] = bytes;
+	g_allocs[p] = {bytes, true};
 	return p;
 }
 
@@ -681,12 +685,43 @@ extern "C" void pim_snappy_host_free(void *p)
 {
 	if (!p)
 		return;
+	bool pinned = true;
 	{
 		std::lock_guard<std::mutex> lk(g_alloc_mu);
-		g_allocs.erase(p);
+		auto it = g_allocs.find(p);
+		if (it != g_allocs.end()) {
+			pinned = it->second.pinned;
+			g_allocs.erase(it);
+		}
 	}
-	cudaFreeHost(p);
+	if (pinned)
+		cudaFreeHost(p);
+	else
+		free(p);
 }
+
+namespace pimsnappy {
+namespace {
+// The buffers setup_compression / setup_decompression hand out (what the reference mallocs, snappy_compress.c:446-447,
+// snappy_decompress.c:206-207).  Page-locking costs about half a millisecond per MB (lock + unlock) and pays only where
+// the copies must run beside the kernels, i.e. for shards that are streamed (> 2 chunks): a 10 MB file spent 12 of its
+// 17 ms in cudaHostAlloc / cudaFreeHost.  Smaller buffers are plain malloc; pim_snappy_host_free() knows which is which.
+void *setup_alloc(size_t bytes)
+{
+	if (bytes == 0)
+		bytes = 1;
+	const uint64_t chunk = chunk_bytes();
+	if (chunk && bytes > 2 * chunk)
+		return pim_snappy_host_alloc(bytes);
+	void *p = malloc(bytes);
+	if (!p)
+		return nullptr;
+	std::lock_guard<std::mutex> lk(g_alloc_mu);
+	g_allocs[p] = {bytes, false};
+	return p;
+}
+} // namespace
+} // namespace pimsnappy
 
 extern "C" int pim_snappy_set_devices(const int *device_ids, int n)
 {
@@ -764,7 +799,7 @@ extern "C" void setup_compression(struct host_buffer_context *input, struct host
 	// be 5n, so the bound is taken for block_size >= 64 and re-checked in snappy_compress_dpu.
 	const size_t n = input->length;
 	const size_t cap = 128 + n + n / 6 + 40 * (n / 64 + 1); // (room for the header beside the streamed path's bound)
-	output->buffer = static_cast<uint8_t *>(pim_snappy_host_alloc(cap));
+	output->buffer = static_cast<uint8_t *>(setup_alloc(cap));
 	output->curr = output->buffer;
 	output->length = 0;
 	runtime->pre = now_s() - t0;
@@ -785,7 +820,7 @@ extern "C" snappy_status setup_decompression(struct host_buffer_context *input, 
 		fprintf(stderr, "Output length is to big: max=%ld len=%d\n", output->max, dlength);
 		return SNAPPY_BUFFER_TOO_SMALL;
 	}
-	output->buffer = static_cast<uint8_t *>(pim_snappy_host_alloc(((size_t)dlength + 7) | 0x7FF));
+	output->buffer = static_cast<uint8_t *>(setup_alloc(((size_t)dlength + 7) | 0x7FF));
 	if (!output->buffer)
 		return SNAPPY_INVALID_INPUT;
 	output->curr = output->buffer;
