@@ -260,8 +260,8 @@ struct Walk {
 // hash).  The reference's loop (:370-398) goes hit -> end of its match -> next hit -> ...; here every lane works out, in
 // parallel and once per pass, where the chain would go after a hit at ITS position (the next hit lane at or above its
 // continuation lane, its insert lane, whether the pass may continue there), and the chain is then followed with one
-// shuffle per pair.  (Round 1 fetched the hit lane's data with a warp reduction and re-derived the rest per pair: 27 % of
-// the kernel's instructions.)
+// shuffle and one branch per pair.  (Round 1 fetched the hit lane's data with a warp reduction and re-derived the rest
+// per pair: 27 % of the kernel's instructions.)
 PW_FN void walk_fast(Walk &w, bool has_ic, bool dense, uint32_t hits, uint32_t inval, uint32_t mynins, uint32_t mybit)
 {
 	(void)mybit;
@@ -270,8 +270,11 @@ PW_FN void walk_fast(Walk &w, bool has_ic, bool dense, uint32_t hits, uint32_t i
 	// continue in this pass after my match if the next pair's insert lane and continuation lane are usable
 	const bool cont = dense && nv != 0u && nv <= (1u << CW_CHAIN_MAX) && ((nv << 1) & ~inval);
 	const uint32_t after = hits & (0u - (nv << 1)); // hit lanes at or above my continuation lane
-	const uint32_t word = (after ? (uint32_t)wp::ffs32(after) - 1u : 32u) | ((nv ? 31u - (uint32_t)wp::clz32(nv) : 0u) << 8) | (cont ? 1u << 16 : 0u) |
-	                      (sat ? 1u << 17 : 0u);
+	const uint32_t nx = after ? (uint32_t)wp::ffs32(after) - 1u : 32u;
+	// bits 0-7: next hit lane (32: none), 8-12: my insert lane, 16: the pass may continue after me, 17: match of >= 16 bytes,
+	// 18: ... and does continue (there is a next hit): the only test inside the loop
+	const uint32_t word = nx | ((nv ? 31u - (uint32_t)wp::clz32(nv) : 0u) << 8) | (cont ? 1u << 16 : 0u) | (sat ? 1u << 17 : 0u) |
+	                      (cont && nx != 32u ? 1u << 18 : 0u);
 	w.V = has_ic ? 1u : 0u;
 	w.H = w.firstbit = w.lastbit = w.satbit = 0;
 	w.insbit = w.V;
@@ -284,32 +287,33 @@ PW_FN void walk_fast(Walk &w, bool has_ic, bool dense, uint32_t hits, uint32_t i
 	}
 	uint32_t cur = (uint32_t)wp::ffs32(ab) - 1u;
 	w.firstbit = 1u << cur;
+	uint32_t x;
 	for (;;) {
 		CW_STAT(2);
-		const uint32_t x = wp::shfl(word, (int)cur);
-		const uint32_t fbit = 1u << cur;
-		w.H |= fbit;
-		w.lastbit = fbit;
-		if (x & (1u << 17)) {
-			CW_STAT(4);
-			w.satbit = fbit;
-			w.outcome = 3;
-			return;
-		}
-		if (!(x & (1u << 16))) {
-			w.outcome = 0;
-			return;
-		}
+		x = wp::shfl(word, (int)cur);
+		w.H |= 1u << cur;
+		if (!(x & (1u << 18)))
+			break;
+		const uint32_t nvb = 1u << ((x >> 8) & 31u);
+		w.V |= nvb;
+		w.insbit = nvb;
+		cur = x & 0xFFu;
+	}
+	w.lastbit = 1u << cur;
+	w.first = (w.V & ~1u) == 0u; // no pair was continued after (an insert lane of a match is lane 3 or higher)
+	if (x & (1u << 17)) { // a match of 16 bytes or more ends the walk (the whole warp extends it)
+		CW_STAT(4);
+		w.satbit = w.lastbit;
+		w.outcome = 3;
+	} else if (!(x & (1u << 16))) {
+		w.outcome = 0;
+	} else { // the pass continues after the last hit but the window holds no further hit: that pair gets a pass of its own
 		const uint32_t nvb = 1u << ((x >> 8) & 31u);
 		w.V |= nvb;
 		w.insbit = nvb;
 		w.first = false;
-		cur = x & 0xFFu;
-		if (cur == 32u) { // the window is exhausted: the pair gets a pass of its own (or the block ends, inval)
-			w.outcome = inval ? 2 : 0;
-			w.redo = !inval;
-			return;
-		}
+		w.outcome = inval ? 2 : 0;
+		w.redo = !inval;
 	}
 }
 
