@@ -114,3 +114,25 @@ def test_block_offsets_walk(P, golden):
     txt, sn = golden["terror2"]
     hlen, dlen, bs, off = P.block_offsets(sn)
     assert (dlen, bs, len(off)) == (105438, 32768, 5) and hlen + int(off[-1]) == sn.size
+
+
+def test_entry_points_fail_loudly_without_a_gpu(P, oracle):
+    """No CPU fallback: on a machine without a usable sm_100 GPU the codec entry points return SNAPPY_INVALID_INPUT and
+    produce nothing, for compression and for decompression (the buffers setup_* hand out for small calls are plain malloc
+    and exist either way; pim_snappy_host_free releases them)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("this is the no-GPU behaviour")
+    L = P.lib()
+    data = np.frombuffer(b"no gpu, no codec " * 100, dtype=np.uint8).copy()
+    inp, out, rt = P.HostBufferContext(), P.HostBufferContext(), P.ProgramRuntime()
+    inp.buffer = inp.curr = data.ctypes.data
+    inp.length, inp.max, out.max = data.size, 2**63, 2**63
+    L.setup_compression(C.byref(inp), C.byref(out), C.byref(rt))
+    assert out.buffer
+    assert L.snappy_compress_dpu(C.byref(inp), C.byref(out), 32768, C.byref(rt)) == P.SNAPPY_INVALID_INPUT
+    L.pim_snappy_host_free(out.buffer)
+    with pytest.raises(P.SnappyError) as e:
+        P.decompress(oracle.compress(data, 32768))
+    assert e.value.status == P.SNAPPY_INVALID_INPUT
+    assert P.device_count() <= 0
