@@ -15,10 +15,15 @@ SRC = [os.path.join(HERE, "warp_emu.cpp"),
 
 
 def build():
+    """$PIM_EMU_DEFINES (e.g. "PIM_CW_WINDOW=1 PIM_CW_CHAIN_MAX=24"): build variants of the kernel source get their own library."""
+    global SO
+    defines = os.environ.get("PIM_EMU_DEFINES", "").split()
+    if defines:
+        SO = os.path.join(HERE, "_build", "libwarp_emu_" + "_".join(d.replace("=", "") for d in defines) + ".so")
     if os.path.exists(SO) and all(os.path.getmtime(SO) >= os.path.getmtime(s) for s in SRC):
         return
     os.makedirs(os.path.dirname(SO), exist_ok=True)
-    subprocess.run(["g++", "-O1", "-g", "-shared", "-fPIC", "-std=c++17", "-DPIM_WARP_EMU", SRC[0], "-o", SO], check=True)
+    subprocess.run(["g++", "-O1", "-g", "-shared", "-fPIC", "-std=c++17", "-DPIM_WARP_EMU", *["-D" + d for d in defines], SRC[0], "-o", SO], check=True)
 
 
 class Emu:
