@@ -50,3 +50,36 @@ def test_mutated_streams_agree_with_the_strict_oracle(P, oracle):
                 rejected += 1
         assert np.array_equal(P.decompress(good), data)  # the device is still healthy
     assert rejected > 250 and accepted + rejected == 600
+
+
+@pytest.mark.gpu
+def test_random_inputs_and_block_sizes_compress_like_the_oracle(P, oracle, golden):
+    """Seeded fuzz of the compressor on the GPU (the same families the CPU warp emulator is fuzzed with, tests/test_compress_emu.py):
+    low-entropy, periodic, run-heavy, text and random data, ragged lengths, block sizes from 1 to 65536 -- byte for byte the
+    oracle's stream, and the round trip gives the input back."""
+    rng = np.random.default_rng(0xB200F)
+    text = golden["world192"][0]
+    for case in range(120):
+        kind = case % 6
+        n = int(rng.integers(1, 200000))
+        if kind == 0:
+            data = rng.integers(0, int(rng.integers(2, 6)), n, dtype=np.uint8)
+        elif kind == 1:
+            per = int(rng.integers(1, 70))
+            data = np.tile(rng.integers(0, 256, per, dtype=np.uint8), n // per + 1)[:n].copy()
+        elif kind == 2:
+            s = int(rng.integers(0, text.size - n))
+            data = text[s:s + n].copy()
+        elif kind == 3:
+            data = np.repeat(rng.integers(0, 256, n // 16 + 1, dtype=np.uint8), rng.integers(1, 40, n // 16 + 1))[:n].copy()
+        elif kind == 4:
+            data = rng.integers(0, 256, n, dtype=np.uint8)
+        else:
+            data = np.concatenate([text[:n // 2], rng.integers(0, 256, n - n // 2, dtype=np.uint8)])
+        bs = int(rng.choice([1, 7, 15, 16, 64, 100, 1000, 4096, 5000, 16384, 20000, 32768, 50000, 65535, 65536]))
+        if data.size // bs > 30000:
+            bs = 4096
+        want = oracle.compress(data, bs)
+        got = P.compress(data, bs)
+        assert got.size == want.size and np.array_equal(got, want), (case, kind, data.size, bs)
+        assert np.array_equal(P.decompress(got), data), (case, kind, data.size, bs)
